@@ -1,0 +1,134 @@
+"""Builds the native pieces in-tree (so the .so files travel with the repo snapshot).
+
+    python -m dmlc_core_b200.build            # everything
+    python -m dmlc_core_b200.build cuda host  # selected targets
+
+Targets
+  cuda    dmlc_core_b200/lib/libdmlc_b200.so      the C ABI + sm_100a kernels (nvcc)
+  host    dmlc_core_b200/lib/libdmlc_b200_host.so the dmlc::Parser<IndexType> C++ layer (g++)
+  gen     dmlc_core_b200/lib/libb200gen.so        synthetic-corpus generators (gcc)
+  emul    tests/_build/libstrtonum_emul.so        host build of strtonum_device.h (test only)
+  oracle  oracle/_build/liboracle.so (+ oracle/_ref when /root/reference is present)
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "dmlc_core_b200")
+LIB = os.path.join(PKG, "lib")
+NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+
+
+def _nvcc():
+    for cand in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def _run(cmd):
+    sys.stderr.write("[build] " + " ".join(cmd) + "\n")
+    env = dict(os.environ)
+    env.pop("CXX", None)
+    env.pop("CC", None)
+    subprocess.check_call(cmd, cwd=ROOT, env=env)
+
+
+def _glob(d, exts):
+    out = []
+    for base, _, files in os.walk(d):
+        for f in files:
+            if f.endswith(exts):
+                out.append(os.path.join(base, f))
+    return out
+
+
+def build_cuda(force=False):
+    os.makedirs(LIB, exist_ok=True)
+    target = os.path.join(LIB, "libdmlc_b200.so")
+    srcs = _glob(os.path.join(PKG, "csrc"), (".cu", ".cuh", ".h")) + \
+        [os.path.join(ROOT, "include", "dmlc_b200_parser.h")]
+    if force or _stale(target, srcs):
+        _run([_nvcc()] + NVCC_ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
+                                      "-shared", "--cudart", "static", "-o", target,
+                                      os.path.join(PKG, "csrc", "b200_parser.cu")])
+    return target
+
+
+def build_host(force=False):
+    os.makedirs(LIB, exist_ok=True)
+    target = os.path.join(LIB, "libdmlc_b200_host.so")
+    src_dir = os.path.join(PKG, "src")
+    if not os.path.isdir(src_dir):
+        return None
+    srcs = _glob(src_dir, (".cc", ".h")) + _glob(os.path.join(PKG, "include"), (".h",))
+    ccs = [s for s in srcs if s.endswith(".cc")]
+    if not ccs:
+        return None
+    if force or _stale(target, srcs + [os.path.join(ROOT, "include", "dmlc_b200_parser.h")]):
+        _run(["g++", "-O2", "-std=c++14", "-fPIC", "-shared", "-pthread", "-Wall",
+              "-I" + os.path.join(PKG, "include"), "-I" + os.path.join(ROOT, "include"),
+              "-o", target] + ccs + ["-L" + LIB, "-ldmlc_b200", "-Wl,-rpath,$ORIGIN", "-ldl"])
+    return target
+
+
+def build_gen(force=False):
+    os.makedirs(LIB, exist_ok=True)
+    target = os.path.join(LIB, "libb200gen.so")
+    src = os.path.join(PKG, "csrc", "datagen.c")
+    if not os.path.exists(src):
+        return None
+    if force or _stale(target, [src]):
+        _run(["gcc", "-O2", "-std=gnu11", "-fPIC", "-shared", "-fopenmp", "-o", target, src, "-lm"])
+    return target
+
+
+def build_emul(force=False):
+    out_dir = os.path.join(ROOT, "tests", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    target = os.path.join(out_dir, "libstrtonum_emul.so")
+    src = os.path.join(ROOT, "tests", "strtonum_emul.cc")
+    if not os.path.exists(src):
+        return None
+    if force or _stale(target, [src, os.path.join(PKG, "csrc", "strtonum_device.h")]):
+        _run(["g++", "-O2", "-msse2", "-ffp-contract=off", "-std=c++14", "-fPIC", "-shared",
+              "-DB200P_HOST_EMULATION", "-I" + os.path.join(PKG, "csrc"), "-o", target, src])
+    return target
+
+
+def build_oracle(force=False):
+    odir = os.path.join(ROOT, "oracle")
+    _run(["make", "-s", "-C", odir, "oracle"])
+    ref = os.path.join(odir, "_ref", "libdmlc_ref.so")
+    if os.path.isdir("/root/reference/src") and (force or _stale(
+            ref, [os.path.join(odir, "ref_shim.cc"), os.path.join(odir, "Makefile")])):
+        _run(["make", "-s", "-C", odir, "ref"])
+    return os.path.join(odir, "_build", "liboracle.so")
+
+
+TARGETS = {"cuda": build_cuda, "host": build_host, "gen": build_gen, "emul": build_emul,
+           "oracle": build_oracle}
+
+
+def build_all(force=False):
+    for name in ("cuda", "gen", "host", "emul", "oracle"):
+        TARGETS[name](force)
+
+
+if __name__ == "__main__":
+    names = [a for a in sys.argv[1:] if not a.startswith("-")]
+    force = "--force" in sys.argv
+    if not names:
+        build_all(force)
+    else:
+        for n in names:
+            TARGETS[n](force)

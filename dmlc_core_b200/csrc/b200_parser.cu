@@ -1,0 +1,567 @@
+/*
+ * Host side of the C ABI declared in include/dmlc_b200_parser.h: buffer management, kernel
+ * launches and the copy/compute pipeline around the kernels of text_kernels.cuh.
+ *
+ * There is deliberately no CPU parsing code in this file or anywhere in the library: without a
+ * usable GPU b200p_create fails with B200P_E_CUDA.
+ */
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/dmlc_b200_parser.h"
+#include "text_kernels.cuh"
+
+namespace b200p {
+
+__global__ void ZeroLabels(float *label, const ChunkSummary *summary, unsigned long long cap) {
+  /* CSV rows without a label column keep label 0.0f (reference csv_parser.h:77) */
+  unsigned long long rows = summary->total[kRows];
+  if (rows > cap) rows = cap;
+  for (unsigned long long i = blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x;
+       i < rows; i += static_cast<unsigned long long>(gridDim.x) * blockDim.x) {
+    label[i] = 0.0f;
+  }
+}
+
+struct Arrays {
+  unsigned long long *offset;
+  float *label;
+  float *weight;
+  unsigned long long *qid;
+  void *field;
+  void *index;
+  float *value;
+  uint64_t cap_rows;  /* rows the row-sized arrays can hold (offset holds cap_rows + 1) */
+  uint64_t cap_nnz;
+  Arrays() { std::memset(this, 0, sizeof(*this)); }
+};
+
+struct Slot {
+  cudaStream_t stream;
+  bool own_stream;
+  uint8_t *h_text;   /* pinned staging (streaming path only) */
+  uint8_t *d_text;
+  uint64_t text_cap;
+  uint32_t *d_counts;
+  uint64_t counts_cap; /* in ranges */
+  ChunkSummary *d_summary;
+  ChunkSummary *h_summary; /* pinned */
+  Arrays dev;
+  Arrays host; /* pinned mirrors (streaming path only) */
+  const uint8_t *text; /* device pointer of the chunk in flight */
+  uint64_t nbytes;
+  bool busy;
+  Slot() { std::memset(this, 0, sizeof(*this)); }
+};
+
+}  // namespace b200p
+
+using namespace b200p;
+
+struct b200p_parser_s {
+  b200p_config cfg;
+  uint32_t range_bytes;
+  int depth;
+  std::vector<Slot> slots;   /* streaming path */
+  Slot resident;             /* device-resident path */
+  bool resident_pending;
+  std::deque<int> in_flight; /* slot ids, oldest first */
+  int lent_slot;             /* slot whose pinned input buffer was handed out, or -1 */
+  int returned_slot;         /* slot whose host arrays the caller currently holds, or -1 */
+  double rows_per_byte, nnz_per_byte; /* densest chunk seen so far: sizes later allocations */
+  uint64_t launches;
+  std::string error;
+};
+
+static thread_local std::string g_create_error;
+
+#define CUDA_TRY(h, expr)                                                              \
+  do {                                                                                 \
+    cudaError_t e_ = (expr);                                                           \
+    if (e_ != cudaSuccess) {                                                           \
+      char buf_[512];                                                                  \
+      std::snprintf(buf_, sizeof(buf_), "CUDA error %s at %s:%d: %s", cudaGetErrorName(e_), \
+                    __FILE__, __LINE__, cudaGetErrorString(e_));                       \
+      (h)->error = buf_;                                                               \
+      return B200P_E_CUDA;                                                             \
+    }                                                                                  \
+  } while (0)
+
+static int Fail(b200p_handle h, int code, const char *msg) {
+  h->error = msg;
+  return code;
+}
+
+/* ------------------------------------------------------------------ buffers ----------------- */
+static void FreeDeviceArrays(Arrays *a) {
+  cudaFree(a->offset); cudaFree(a->label); cudaFree(a->weight); cudaFree(a->qid);
+  cudaFree(a->field); cudaFree(a->index); cudaFree(a->value);
+  *a = Arrays();
+}
+static void FreeHostArrays(Arrays *a) {
+  cudaFreeHost(a->offset); cudaFreeHost(a->label); cudaFreeHost(a->weight); cudaFreeHost(a->qid);
+  cudaFreeHost(a->field); cudaFreeHost(a->index); cudaFreeHost(a->value);
+  *a = Arrays();
+}
+
+template <typename T>
+static cudaError_t AllocOne(T **p, uint64_t count, size_t elt, bool pinned) {
+  void *v = NULL;
+  cudaError_t e = pinned ? cudaHostAlloc(&v, std::max<uint64_t>(count, 1) * elt, cudaHostAllocDefault)
+                         : cudaMalloc(&v, std::max<uint64_t>(count, 1) * elt);
+  *p = static_cast<T *>(v);
+  return e;
+}
+
+/* (Re)allocate so that `rows` rows and `nnz` entries fit. Caller has synchronised the stream. */
+static int EnsureArrays(b200p_handle h, Arrays *a, uint64_t rows, uint64_t nnz, bool pinned) {
+  const int fmt = h->cfg.format;
+  const size_t iw = h->cfg.index_bytes;
+  if (rows > a->cap_rows || a->offset == NULL) {
+    const uint64_t cap = rows + rows / 4 + 1024;
+    if (pinned) {
+      cudaFreeHost(a->offset); cudaFreeHost(a->label); cudaFreeHost(a->weight); cudaFreeHost(a->qid);
+    } else {
+      cudaFree(a->offset); cudaFree(a->label); cudaFree(a->weight); cudaFree(a->qid);
+    }
+    a->offset = NULL; a->label = NULL; a->weight = NULL; a->qid = NULL; a->cap_rows = 0;
+    CUDA_TRY(h, AllocOne(&a->offset, cap + 1, 8, pinned));
+    CUDA_TRY(h, AllocOne(&a->label, cap, 4, pinned));
+    if (fmt != B200P_FORMAT_CSV) CUDA_TRY(h, AllocOne(&a->weight, cap, 4, pinned));
+    if (fmt == B200P_FORMAT_LIBSVM) CUDA_TRY(h, AllocOne(&a->qid, cap, 8, pinned));
+    a->cap_rows = cap;
+  }
+  if (nnz > a->cap_nnz || a->index == NULL) {
+    const uint64_t cap = nnz + nnz / 4 + 1024;
+    if (pinned) {
+      cudaFreeHost(a->field); cudaFreeHost(a->index); cudaFreeHost(a->value);
+    } else {
+      cudaFree(a->field); cudaFree(a->index); cudaFree(a->value);
+    }
+    a->field = NULL; a->index = NULL; a->value = NULL; a->cap_nnz = 0;
+    if (fmt == B200P_FORMAT_LIBFM) CUDA_TRY(h, AllocOne(reinterpret_cast<char **>(&a->field), cap, iw, pinned));
+    CUDA_TRY(h, AllocOne(reinterpret_cast<char **>(&a->index), cap, iw, pinned));
+    CUDA_TRY(h, AllocOne(&a->value, cap, 4, pinned));
+    a->cap_nnz = cap;
+  }
+  return B200P_OK;
+}
+
+/* Output capacity to provision for a chunk of `nbytes` before its counts are known. */
+static void Provision(const b200p_handle h, uint64_t nbytes, uint64_t *rows, uint64_t *nnz) {
+  if (h->nnz_per_byte > 0.0) {
+    *rows = static_cast<uint64_t>(h->rows_per_byte * 1.25 * nbytes) + 1024;
+    *nnz = static_cast<uint64_t>(h->nnz_per_byte * 1.25 * nbytes) + 1024;
+  } else {
+    *rows = nbytes / 32 + 1024; /* first chunk: a guess; pass 2 is re-run if it was too small */
+    *nnz = nbytes / 4 + 1024;
+  }
+}
+
+/* ------------------------------------------------------------------ launches ---------------- */
+template <int FMT, typename IdxT>
+static void LaunchWalks(const WalkParams &p, cudaStream_t s, bool emit) {
+  const unsigned grid = (p.num_ranges + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (emit) {
+    WalkText<FMT, IdxT, true><<<grid, kCtaThreads, 0, s>>>(p);
+  } else {
+    WalkText<FMT, IdxT, false><<<grid, kCtaThreads, 0, s>>>(p);
+  }
+}
+
+static void LaunchWalk(const b200p_handle h, const WalkParams &p, cudaStream_t s, bool emit) {
+  const bool wide = h->cfg.index_bytes == 8;
+  switch (h->cfg.format) {
+    case B200P_FORMAT_LIBSVM:
+      if (wide) LaunchWalks<kLibSVM, uint64_t>(p, s, emit); else LaunchWalks<kLibSVM, uint32_t>(p, s, emit);
+      break;
+    case B200P_FORMAT_LIBFM:
+      if (wide) LaunchWalks<kLibFM, uint64_t>(p, s, emit); else LaunchWalks<kLibFM, uint32_t>(p, s, emit);
+      break;
+    default:
+      if (wide) LaunchWalks<kCSV, uint64_t>(p, s, emit); else LaunchWalks<kCSV, uint32_t>(p, s, emit);
+      break;
+  }
+}
+
+static WalkParams MakeParams(const b200p_handle h, const Slot &s) {
+  WalkParams p;
+  std::memset(&p, 0, sizeof(p));
+  p.text = s.text;
+  p.size = static_cast<uint32_t>(s.nbytes);
+  p.range_bytes = h->range_bytes;
+  p.num_ranges = static_cast<uint32_t>((s.nbytes + h->range_bytes - 1) / h->range_bytes);
+  p.label_column = h->cfg.label_column;
+  p.counts = s.d_counts;
+  p.summary = s.d_summary;
+  p.offset = s.dev.offset;
+  p.label = s.dev.label;
+  p.weight = s.dev.weight;
+  p.qid = s.dev.qid;
+  p.field = s.dev.field;
+  p.index = s.dev.index;
+  p.value = s.dev.value;
+  p.cap_rows = s.dev.cap_rows;
+  p.cap_nnz = s.dev.cap_nnz;
+  return p;
+}
+
+/* pass 2 (+ the CSV label clear), then the summary travels to the host */
+static int EnqueueEmit(b200p_handle h, Slot *s) {
+  const WalkParams p = MakeParams(h, *s);
+  if (h->cfg.format == B200P_FORMAT_CSV) {
+    ZeroLabels<<<296, 256, 0, s->stream>>>(s->dev.label, s->d_summary, s->dev.cap_rows);
+    ++h->launches;
+  }
+  LaunchWalk(h, p, s->stream, true);
+  ++h->launches;
+  CUDA_TRY(h, cudaGetLastError());
+  CUDA_TRY(h, cudaMemcpyAsync(s->h_summary, s->d_summary, sizeof(ChunkSummary),
+                              cudaMemcpyDeviceToHost, s->stream));
+  return B200P_OK;
+}
+
+/* pass 1 + scan + (speculative) pass 2 for the chunk described by s->text / s->nbytes */
+static int EnqueueParse(b200p_handle h, Slot *s) {
+  if (s->nbytes == 0) {
+    std::memset(s->h_summary, 0, sizeof(ChunkSummary));
+    return B200P_OK;
+  }
+  const uint64_t ranges = (s->nbytes + h->range_bytes - 1) / h->range_bytes;
+  if (ranges > s->counts_cap) {
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+    cudaFree(s->d_counts);
+    s->d_counts = NULL;
+    s->counts_cap = 0;
+    const uint64_t cap = ranges + ranges / 4 + 64;
+    CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&s->d_counts), cap * kNumCounters * sizeof(uint32_t)));
+    s->counts_cap = cap;
+  }
+  uint64_t want_rows, want_nnz;
+  Provision(h, s->nbytes, &want_rows, &want_nnz);
+  if (want_rows > s->dev.cap_rows || want_nnz > s->dev.cap_nnz || s->dev.offset == NULL) {
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+    const int rc = EnsureArrays(h, &s->dev, want_rows, want_nnz, false);
+    if (rc != B200P_OK) return rc;
+  }
+  const WalkParams p = MakeParams(h, *s);
+  LaunchWalk(h, p, s->stream, false);
+  ScanRanges<<<1, 1024, 0, s->stream>>>(s->d_counts, p.num_ranges, s->d_summary);
+  h->launches += 2;
+  CUDA_TRY(h, cudaGetLastError());
+  return EnqueueEmit(h, s);
+}
+
+/* Wait for the chunk, re-run pass 2 with larger arrays if the provision was too small, and
+   translate device error bits. On success the device arrays of `s` hold the chunk. */
+static int FinishParse(b200p_handle h, Slot *s) {
+  if (s->nbytes == 0) return B200P_OK;
+  CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+  const ChunkSummary &sum = *s->h_summary;
+  if (sum.total[kRows] > s->dev.cap_rows || sum.total[kNnz] > s->dev.cap_nnz) {
+    const int rc = EnsureArrays(h, &s->dev, sum.total[kRows], sum.total[kNnz], false);
+    if (rc != B200P_OK) return rc;
+    const int rc2 = EnqueueEmit(h, s);
+    if (rc2 != B200P_OK) return rc2;
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+  }
+  h->rows_per_byte = std::max(h->rows_per_byte, static_cast<double>(sum.total[kRows]) / s->nbytes);
+  h->nnz_per_byte = std::max(h->nnz_per_byte, static_cast<double>(sum.total[kNnz]) / s->nbytes);
+  if (sum.error & kErrNegativeIndex) {
+    return Fail(h, B200P_E_PARSE, "Check failed: sign == true (negative value in an unsigned index/field)");
+  }
+  if (sum.error & kErrValueCount) {
+    return Fail(h, B200P_E_PARSE,
+                "Check failed: offset.back() == value.size() || value.size() == 0");
+  }
+  return B200P_OK;
+}
+
+static void FillBlock(const b200p_handle h, const Slot &s, const Arrays &a, bool on_device,
+                      b200p_rowblock *out) {
+  std::memset(out, 0, sizeof(*out));
+  out->index_bytes = h->cfg.index_bytes;
+  out->on_device = on_device ? 1 : 0;
+  out->text_bytes = s.nbytes;
+  if (s.nbytes == 0) return;
+  const ChunkSummary &sum = *s.h_summary;
+  out->rows = sum.total[kRows];
+  out->nnz = sum.total[kNnz];
+  out->n_weight = sum.total[kWeights];
+  out->n_qid = sum.total[kQids];
+  out->n_value = sum.total[kValues];
+  out->n_field = h->cfg.format == B200P_FORMAT_LIBFM ? out->nnz : 0;
+  if (out->rows == 0) return;
+  out->offset = reinterpret_cast<const uint64_t *>(a.offset);
+  out->label = a.label;
+  out->weight = out->n_weight ? a.weight : NULL;
+  out->qid = out->n_qid ? reinterpret_cast<const uint64_t *>(a.qid) : NULL;
+  out->field = out->n_field ? a.field : NULL;
+  out->index = out->nnz ? a.index : NULL;
+  out->value = out->n_value ? a.value : NULL;
+}
+
+static void DestroySlot(Slot *s) {
+  if (s->stream != NULL) cudaStreamSynchronize(s->stream);
+  cudaFreeHost(s->h_text);
+  cudaFree(s->d_text);
+  cudaFree(s->d_counts);
+  cudaFree(s->d_summary);
+  cudaFreeHost(s->h_summary);
+  FreeDeviceArrays(&s->dev);
+  FreeHostArrays(&s->host);
+  if (s->own_stream && s->stream != NULL) cudaStreamDestroy(s->stream);
+  *s = Slot();
+}
+
+static int InitSlot(b200p_handle h, Slot *s, cudaStream_t stream) {
+  if (stream != NULL) {
+    s->stream = stream;
+    s->own_stream = false;
+  } else {
+    CUDA_TRY(h, cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    s->own_stream = true;
+  }
+  CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&s->d_summary), sizeof(ChunkSummary)));
+  CUDA_TRY(h, cudaHostAlloc(reinterpret_cast<void **>(&s->h_summary), sizeof(ChunkSummary), cudaHostAllocDefault));
+  std::memset(s->h_summary, 0, sizeof(ChunkSummary));
+  return B200P_OK;
+}
+
+/* ------------------------------------------------------------------ C ABI ------------------- */
+extern "C" {
+
+const char *b200p_version(void) { return "dmlc_b200 0.1 sm_100a"; }
+
+const char *b200p_last_error(b200p_handle h) {
+  return h != NULL ? h->error.c_str() : g_create_error.c_str();
+}
+
+int b200p_create(const b200p_config *config, b200p_handle *out) {
+  if (out == NULL) return B200P_E_INVALID;
+  *out = NULL;
+  if (config == NULL || config->format < 0 || config->format > 2 ||
+      (config->index_bytes != 4 && config->index_bytes != 8)) {
+    g_create_error = "b200p_create: format must be 0..2 and index_bytes 4 or 8";
+    return B200P_E_INVALID;
+  }
+  b200p_handle h = new (std::nothrow) b200p_parser_s();
+  if (h == NULL) return B200P_E_INVALID;
+  h->cfg = *config;
+  if (h->cfg.chunk_bytes == 0) h->cfg.chunk_bytes = 64ull << 20;
+  if (h->cfg.chunk_bytes > B200P_MAX_CHUNK_BYTES) h->cfg.chunk_bytes = B200P_MAX_CHUNK_BYTES;
+  uint32_t rb = config->range_bytes > 0 ? static_cast<uint32_t>(config->range_bytes) : 8192u;
+  rb = std::max<uint32_t>(kStepBytes, (rb + kStepBytes - 1) / kStepBytes * kStepBytes);
+  h->range_bytes = rb;
+  h->depth = config->depth > 0 ? std::min(config->depth, 8) : 3;
+  h->lent_slot = -1;
+  h->returned_slot = -1;
+  h->resident_pending = false;
+  h->rows_per_byte = h->nnz_per_byte = 0.0;
+  h->launches = 0;
+
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count <= 0 || config->device < 0 || config->device >= count) {
+    char buf[256];
+    std::snprintf(buf, sizeof(buf),
+                  "b200p_create: no usable CUDA device %d (%s); this library has no CPU path",
+                  config->device, e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0 or ordinal out of range");
+    g_create_error = buf;
+    delete h;
+    return B200P_E_CUDA;
+  }
+  e = cudaSetDevice(config->device);
+  int rc = B200P_OK;
+  if (e != cudaSuccess) {
+    g_create_error = std::string("b200p_create: cudaSetDevice failed: ") + cudaGetErrorString(e);
+    delete h;
+    return B200P_E_CUDA;
+  }
+  rc = InitSlot(h, &h->resident, static_cast<cudaStream_t>(config->stream));
+  if (rc != B200P_OK) {
+    g_create_error = h->error;
+    DestroySlot(&h->resident);
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return B200P_OK;
+}
+
+void b200p_destroy(b200p_handle h) {
+  if (h == NULL) return;
+  cudaSetDevice(h->cfg.device);
+  for (size_t i = 0; i < h->slots.size(); ++i) DestroySlot(&h->slots[i]);
+  DestroySlot(&h->resident);
+  delete h;
+}
+
+uint64_t b200p_launch_count(b200p_handle h) { return h != NULL ? h->launches : 0; }
+
+/* ---- device-resident path ---- */
+int b200p_parse_device_async(b200p_handle h, const void *d_text, uint64_t nbytes) {
+  if (h == NULL) return B200P_E_INVALID;
+  if (nbytes > B200P_MAX_CHUNK_BYTES) return Fail(h, B200P_E_INVALID, "chunk larger than B200P_MAX_CHUNK_BYTES");
+  if ((reinterpret_cast<uintptr_t>(d_text) & 15u) != 0) return Fail(h, B200P_E_INVALID, "device chunk must be 16-byte aligned");
+  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  Slot *s = &h->resident;
+  s->text = static_cast<const uint8_t *>(d_text);
+  s->nbytes = nbytes;
+  h->resident_pending = true;
+  return EnqueueParse(h, s);
+}
+
+int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out) {
+  if (h == NULL || out == NULL) return B200P_E_INVALID;
+  if (!h->resident_pending) return Fail(h, B200P_E_EMPTY, "b200p_parse_device_finish without a pending chunk");
+  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  h->resident_pending = false;
+  const int rc = FinishParse(h, &h->resident);
+  if (rc != B200P_OK) return rc;
+  FillBlock(h, h->resident, h->resident.dev, true, out);
+  return B200P_OK;
+}
+
+int b200p_parse_device(b200p_handle h, const void *d_text, uint64_t nbytes, b200p_rowblock *out) {
+  const int rc = b200p_parse_device_async(h, d_text, nbytes);
+  if (rc != B200P_OK) return rc;
+  return b200p_parse_device_finish(h, out);
+}
+
+int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t nbytes) {
+  if (h == NULL || (nbytes != 0 && (host_dst == NULL || device_src == NULL))) return B200P_E_INVALID;
+  if (nbytes == 0) return B200P_OK;
+  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  CUDA_TRY(h, cudaMemcpyAsync(host_dst, device_src, nbytes, cudaMemcpyDeviceToHost, h->resident.stream));
+  CUDA_TRY(h, cudaStreamSynchronize(h->resident.stream));
+  return B200P_OK;
+}
+
+/* ---- streaming path ---- */
+static int FreeSlotIndex(b200p_handle h) {
+  /* slots are created on demand up to depth; the one whose arrays the caller still holds
+     (returned_slot) is not reusable until the next b200p_next */
+  for (size_t i = 0; i < h->slots.size(); ++i) {
+    if (!h->slots[i].busy && static_cast<int>(i) != h->returned_slot) return static_cast<int>(i);
+  }
+  if (static_cast<int>(h->slots.size()) < h->depth + 1) {
+    h->slots.push_back(Slot());
+    return static_cast<int>(h->slots.size()) - 1;
+  }
+  return -1;
+}
+
+static int PrepareSlot(b200p_handle h, int id, uint64_t nbytes) {
+  Slot *s = &h->slots[id];
+  if (s->stream == NULL) {
+    const int rc = InitSlot(h, s, NULL);
+    if (rc != B200P_OK) return rc;
+  }
+  const uint64_t want = std::max<uint64_t>(nbytes, h->cfg.chunk_bytes);
+  if (want > s->text_cap) {
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+    cudaFreeHost(s->h_text);
+    cudaFree(s->d_text);
+    s->h_text = NULL;
+    s->d_text = NULL;
+    s->text_cap = 0;
+    const uint64_t cap = (want + 4095) / 4096 * 4096;
+    CUDA_TRY(h, cudaHostAlloc(reinterpret_cast<void **>(&s->h_text), cap, cudaHostAllocDefault));
+    CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&s->d_text), cap));
+    s->text_cap = cap;
+  }
+  return B200P_OK;
+}
+
+int b200p_input_buffer(b200p_handle h, void **host_ptr, uint64_t *capacity) {
+  if (h == NULL || host_ptr == NULL) return B200P_E_INVALID;
+  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  if (h->lent_slot < 0) {
+    const int id = FreeSlotIndex(h);
+    if (id < 0) return Fail(h, B200P_E_AGAIN, "all pipeline slots are in flight: call b200p_next");
+    const int rc = PrepareSlot(h, id, 0);
+    if (rc != B200P_OK) return rc;
+    h->lent_slot = id;
+  }
+  *host_ptr = h->slots[h->lent_slot].h_text;
+  if (capacity != NULL) *capacity = h->slots[h->lent_slot].text_cap;
+  return B200P_OK;
+}
+
+int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes) {
+  if (h == NULL || (text == NULL && nbytes != 0)) return B200P_E_INVALID;
+  if (nbytes > B200P_MAX_CHUNK_BYTES) return Fail(h, B200P_E_INVALID, "chunk larger than B200P_MAX_CHUNK_BYTES");
+  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  int id = h->lent_slot;
+  const bool in_place = id >= 0 && text == h->slots[id].h_text;
+  if (id < 0) {
+    id = FreeSlotIndex(h);
+    if (id < 0) return Fail(h, B200P_E_AGAIN, "all pipeline slots are in flight: call b200p_next");
+  }
+  if (in_place && nbytes > h->slots[id].text_cap) return Fail(h, B200P_E_INVALID, "chunk exceeds the staging buffer");
+  if (!in_place) {
+    const int rc = PrepareSlot(h, id, nbytes);
+    if (rc != B200P_OK) return rc;
+    if (nbytes != 0) std::memcpy(h->slots[id].h_text, text, nbytes);
+  }
+  h->lent_slot = -1;
+  Slot *s = &h->slots[id];
+  s->nbytes = nbytes;
+  s->text = s->d_text;
+  if (nbytes != 0) {
+    CUDA_TRY(h, cudaMemcpyAsync(s->d_text, s->h_text, nbytes, cudaMemcpyHostToDevice, s->stream));
+  }
+  const int rc = EnqueueParse(h, s);
+  if (rc != B200P_OK) return rc;
+  s->busy = true;
+  h->in_flight.push_back(id);
+  return B200P_OK;
+}
+
+int b200p_pending(b200p_handle h) { return h != NULL ? static_cast<int>(h->in_flight.size()) : 0; }
+
+int b200p_next(b200p_handle h, b200p_rowblock *out) {
+  if (h == NULL || out == NULL) return B200P_E_INVALID;
+  if (h->in_flight.empty()) return Fail(h, B200P_E_EMPTY, "b200p_next: nothing submitted");
+  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  const int id = h->in_flight.front();
+  h->in_flight.pop_front();
+  Slot *s = &h->slots[id];
+  s->busy = false;
+  h->returned_slot = -1; /* the block handed out before this call is released now */
+  int rc = FinishParse(h, s);
+  if (rc != B200P_OK) return rc;
+  if (s->nbytes != 0) {
+    const ChunkSummary &sum = *s->h_summary;
+    const uint64_t rows = sum.total[kRows], nnz = sum.total[kNnz];
+    rc = EnsureArrays(h, &s->host, rows, nnz, true);
+    if (rc != B200P_OK) return rc;
+    const size_t iw = h->cfg.index_bytes;
+    cudaStream_t st = s->stream;
+    if (rows != 0) {
+      CUDA_TRY(h, cudaMemcpyAsync(s->host.offset, s->dev.offset, (rows + 1) * 8, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(h, cudaMemcpyAsync(s->host.label, s->dev.label, rows * 4, cudaMemcpyDeviceToHost, st));
+      if (sum.total[kWeights] != 0) CUDA_TRY(h, cudaMemcpyAsync(s->host.weight, s->dev.weight, sum.total[kWeights] * 4, cudaMemcpyDeviceToHost, st));
+      if (sum.total[kQids] != 0) CUDA_TRY(h, cudaMemcpyAsync(s->host.qid, s->dev.qid, sum.total[kQids] * 8, cudaMemcpyDeviceToHost, st));
+      if (nnz != 0) {
+        CUDA_TRY(h, cudaMemcpyAsync(s->host.index, s->dev.index, nnz * iw, cudaMemcpyDeviceToHost, st));
+        if (h->cfg.format == B200P_FORMAT_LIBFM) CUDA_TRY(h, cudaMemcpyAsync(s->host.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
+      }
+      if (sum.total[kValues] != 0) CUDA_TRY(h, cudaMemcpyAsync(s->host.value, s->dev.value, sum.total[kValues] * 4, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(h, cudaStreamSynchronize(st));
+    }
+  }
+  FillBlock(h, *s, s->host, false, out);
+  h->returned_slot = id;
+  return B200P_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,720 @@
+/*
+ * sm_100a kernels that turn one chunk of LibSVM / LibFM / CSV text, resident in HBM, into the
+ * CSR arrays of a dmlc RowBlock.  They replace the CPU work of
+ *   TextParserBase::FillData         reference src/data/text_parser.h:93-134
+ *   LibSVMParser::ParseBlock         reference src/data/libsvm_parser.h:35-99
+ *   LibFMParser::ParseBlock          reference src/data/libfm_parser.h:35-93
+ *   CSVParser::ParseBlock            reference src/data/csv_parser.h:63-104
+ * and are bit-exact with them (oracle: oracle/dmlc_oracle.c, oracle/_ref).
+ *
+ * Shape of the computation (HBM-bound byte work, no tensor cores):
+ *
+ *   pass 1  WalkText<..., EMIT=false>   count rows / nnz / values / weights / qids per byte range
+ *   scan    ScanRanges                  exclusive prefix over ranges -> where each range writes
+ *   pass 2  WalkText<..., EMIT=true>    same walk, now converting tokens and storing CSR arrays
+ *
+ * The chunk is cut into fixed byte ranges; a warp owns the lines that START inside its range
+ * (the reference slices a chunk the same way for its OpenMP team, text_parser.h:104-118), so no
+ * parsing state ever crosses a range.  Inside a range the warp streams 512-byte steps: every
+ * lane loads 16 contiguous bytes (one coalesced 512 B request per warp), classifies them with
+ * SWAR arithmetic into digit-run / end-of-line bit masks, and the starts of digit runs
+ * ("tokens") are compacted into a per-warp queue in shared memory.  Tokens are then handled 32
+ * at a time, one per lane: a short backward look at the separator decides whether the token is
+ * bound by ':' to the previous one, and warp ballots + popc/clz turn those flags into chain
+ * positions, roles (label / weight / qid / field / index / value), row ids and output slots --
+ * the exact pairing rules of ParsePair / ParseTriple (reference src/data/strtonum.h:227-303).
+ * Tokens of one role are queued again so that conversion always runs with 32 busy lanes doing
+ * the same arithmetic, and every store is 32 consecutive elements of one CSR array.
+ */
+#ifndef DMLC_CORE_B200_TEXT_KERNELS_CUH_
+#define DMLC_CORE_B200_TEXT_KERNELS_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "strtonum_device.h"
+
+namespace b200p {
+
+enum Format { kLibSVM = 0, kLibFM = 1, kCSV = 2 };
+
+/* counters carried per range through the scan; order fixed (index into arrays below) */
+enum Counter { kRows = 0, kNnz = 1, kValues = 2, kWeights = 3, kQids = 4, kNumCounters = 5 };
+
+/* error bits surfaced to the host (-> dmlc::Error in the C++ layer) */
+enum ErrorBits {
+  kErrNegativeIndex = 1u,   /* reference strtonum.h:141  CHECK_EQ(sign, true) */
+  kErrValueCount = 2u,      /* reference row_block.h:177 offset.back()==value.size()||empty */
+  kErrCapacity = 4u,        /* output buffers too small: host grows them and re-runs pass 2 */
+};
+
+constexpr int kStepBytes = 512;        /* one warp step: 32 lanes x 16 B */
+constexpr int kWarpsPerCta = 8;
+constexpr int kCtaThreads = kWarpsPerCta * 32;
+constexpr int kTokenQueue = 320;       /* < 32 left over + <= 256 new digit runs per step */
+constexpr int kFieldQueue = 576;       /* CSV: < 32 left over + <= 512 field starts per step */
+constexpr int kRoleQueue = 64;         /* < 32 left over + <= 32 new per token group */
+
+/* Result header written by ScanRanges (device memory, copied to the host per chunk). */
+struct ChunkSummary {
+  unsigned long long total[kNumCounters];
+  unsigned int error;
+  unsigned int ranges;
+};
+
+struct WalkParams {
+  const uint8_t *text;     /* 16-byte aligned */
+  uint32_t size;           /* bytes, < 2^31 */
+  uint32_t range_bytes;    /* multiple of kStepBytes */
+  uint32_t num_ranges;
+  int32_t label_column;    /* CSV */
+  uint32_t *counts;        /* [kNumCounters][num_ranges]: pass 1 writes counts, scan rewrites
+                              them in place as exclusive prefixes, pass 2 reads them */
+  ChunkSummary *summary;
+  /* outputs (pass 2) and their capacities in elements */
+  unsigned long long *offset;
+  float *label;
+  float *weight;
+  unsigned long long *qid;
+  void *field;
+  void *index;
+  float *value;
+  unsigned long long cap_rows;
+  unsigned long long cap_nnz;
+};
+
+/* ---------------------------------------------------------------- SWAR byte classes -------- */
+/* All helpers take xm = word & 0x7f7f7f7f and return a word whose bit 7 of each byte is the
+   predicate; bytes >= 0x80 are removed by the caller with & ~word. */
+__device__ __forceinline__ uint32_t ByteEq(uint32_t xm, uint32_t c) {
+  return ~((xm ^ (c * 0x01010101u)) + 0x7f7f7f7fu);
+}
+__device__ __forceinline__ uint32_t ByteGe(uint32_t xm, uint32_t c) {
+  return xm + ((0x80u - c) * 0x01010101u);
+}
+/* bit 7 of each byte -> 4 adjacent bits */
+__device__ __forceinline__ uint32_t Gather4(uint32_t m) {
+  return (((m & 0x80808080u) >> 7) * 0x00204081u >> 21) & 0xFu;
+}
+
+__device__ __forceinline__ uint32_t WordDigitChar(uint32_t w) {
+  const uint32_t xm = w & 0x7f7f7f7fu;
+  const uint32_t in_range = ByteGe(xm, 0x2Bu) & ~ByteGe(xm, 0x3Au);      /* '+' .. '9' */
+  const uint32_t not_sep = ~(ByteEq(xm, ',') | ByteEq(xm, '/'));
+  const uint32_t is_e = ~(((xm | 0x20202020u) ^ 0x65656565u) + 0x7f7f7f7fu);
+  return ((in_range & not_sep) | is_e) & ~w;
+}
+__device__ __forceinline__ uint32_t WordEol(uint32_t w) {
+  const uint32_t xm = w & 0x7f7f7f7fu;
+  return (ByteEq(xm, '\n') | ByteEq(xm, '\r')) & ~w;
+}
+__device__ __forceinline__ uint32_t WordComma(uint32_t w) {
+  const uint32_t xm = w & 0x7f7f7f7fu;
+  return ByteEq(xm, ',') & ~w;
+}
+
+struct Masks16 {
+  uint32_t a;  /* digit-run bytes (LibSVM/LibFM) or commas (CSV) */
+  uint32_t eol;
+};
+
+template <int FMT>
+__device__ __forceinline__ Masks16 Classify(const uint4 v) {
+  Masks16 m;
+  if (FMT == kCSV) {
+    m.a = Gather4(WordComma(v.x)) | (Gather4(WordComma(v.y)) << 4) |
+          (Gather4(WordComma(v.z)) << 8) | (Gather4(WordComma(v.w)) << 12);
+  } else {
+    m.a = Gather4(WordDigitChar(v.x)) | (Gather4(WordDigitChar(v.y)) << 4) |
+          (Gather4(WordDigitChar(v.z)) << 8) | (Gather4(WordDigitChar(v.w)) << 12);
+  }
+  m.eol = Gather4(WordEol(v.x)) | (Gather4(WordEol(v.y)) << 4) | (Gather4(WordEol(v.z)) << 8) |
+          (Gather4(WordEol(v.w)) << 12);
+  return m;
+}
+
+/* 16 bytes at `pos` (multiple of 16); bytes at or past `size` read as NUL */
+__device__ __forceinline__ uint4 Load16(const uint8_t *text, uint32_t size, uint32_t pos) {
+  if (pos + 16u <= size) {
+    return __ldg(reinterpret_cast<const uint4 *>(text + pos));
+  }
+  uint32_t w[4] = {0u, 0u, 0u, 0u};
+  for (uint32_t i = 0; i < 16u; ++i) {
+    if (pos + i < size) w[i >> 2] |= static_cast<uint32_t>(text[pos + i]) << ((i & 3u) * 8u);
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+/* bits [lo, hi) of a lane's 16-bit mask, for absolute byte bounds against the lane's first byte */
+__device__ __forceinline__ uint32_t KeepMask(uint32_t lane_first, uint32_t from, uint32_t to) {
+  const uint32_t lo = from > lane_first ? min(from - lane_first, 16u) : 0u;
+  const uint32_t hi = to > lane_first ? min(to - lane_first, 16u) : 0u;
+  return ((1u << hi) - 1u) & ~((1u << lo) - 1u);
+}
+
+__device__ __forceinline__ uint32_t LaneMaskLt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+__device__ __forceinline__ uint32_t LaneMaskLe() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_le;" : "=r"(m));
+  return m;
+}
+
+/* inclusive warp prefix sum of small non-negative ints */
+__device__ __forceinline__ uint32_t WarpInclusiveSum(uint32_t v, int lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane >= d) v += o;
+  }
+  return v;
+}
+
+/* first end-of-line byte in [from, to): returns its position, or 0xffffffff */
+__device__ uint32_t FindEol(const uint8_t *text, uint32_t size, uint32_t from, uint32_t to,
+                            int lane) {
+  if (to > size) to = size;
+  for (uint32_t base = from & ~uint32_t(kStepBytes - 1); base < to; base += kStepBytes) {
+    const uint32_t first = base + 16u * lane;
+    const uint4 v = Load16(text, size, first);
+    uint32_t e = Gather4(WordEol(v.x)) | (Gather4(WordEol(v.y)) << 4) |
+                 (Gather4(WordEol(v.z)) << 8) | (Gather4(WordEol(v.w)) << 12);
+    e &= KeepMask(first, from, to);
+    const uint32_t who = __ballot_sync(0xffffffffu, e != 0u);
+    if (who != 0u) {
+      const int src = __ffs(who) - 1;
+      const uint32_t es = __shfl_sync(0xffffffffu, e, src);
+      return base + 16u * src + (__ffs(es) - 1);
+    }
+  }
+  return 0xffffffffu;
+}
+
+/* ------------------------------------------------------------------ per-warp scratch -------- */
+template <int FMT>
+struct WarpScratch {
+  uint32_t tokens[FMT == kCSV ? kFieldQueue : kTokenQueue];
+  /* role queues (pass 2): LibSVM/LibFM use label, weight, qid, index, value (+ field);
+     CSV converts straight out of the token queue and uses none of them */
+  uint32_t q_label[FMT == kCSV ? 1 : kRoleQueue];
+  uint32_t q_weight[FMT == kCSV ? 1 : kRoleQueue];
+  uint32_t q_qid[FMT == kLibSVM ? kRoleQueue : 1];
+  uint32_t q_field[FMT == kLibFM ? kRoleQueue : 1];
+  uint32_t q_index[FMT == kCSV ? 1 : kRoleQueue];
+  uint32_t q_value[FMT == kCSV ? 1 : kRoleQueue];
+};
+
+/* State of one warp while it walks its range. All members are warp-uniform. */
+struct WalkState {
+  uint32_t seen[kNumCounters];  /* pass 1: counts so far; pass 2: absolute output cursors for
+                                   the *role pass* (offset/label row ids, nnz ids) */
+  /* chain context of the last token handled (ParsePair/ParseTriple pairing) */
+  int carry_pos;        /* position of that token in its ':'-bound chain (1-based) */
+  bool carry_first;     /* chain is the first one on its line (label[:weight]...) */
+  uint32_t carry_at;    /* byte position of that token */
+  uint32_t carry_col;   /* CSV: column of the last field handled */
+  /* pass 2: role queues fill levels and how many elements of each array were stored */
+  uint32_t n_label, n_weight, n_qid, n_index, n_value;
+  uint32_t w_label, w_weight, w_qid, w_index, w_value;
+  uint32_t error;
+};
+
+template <typename IdxT>
+__device__ __forceinline__ void StoreIdx(void *base, uint32_t at, uint64_t v) {
+  reinterpret_cast<IdxT *>(base)[at] = static_cast<IdxT>(v);
+}
+
+/* Drain helper: lanes [0, take) pop queue entries and run `conv`; the rest of the queue moves
+   to the front. `take` is 32 in steady state, smaller only at the final flush. */
+__device__ __forceinline__ void QueuePop(uint32_t *q, uint32_t &fill, uint32_t take, int lane) {
+  const uint32_t rest = fill - take;
+  uint32_t moved = 0;
+  if (lane < rest) moved = q[take + lane];
+  __syncwarp();
+  if (lane < rest) q[lane] = moved;
+  __syncwarp();
+  fill = rest;
+}
+
+template <int FMT, typename IdxT>
+__device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Text &txt,
+                                                WarpScratch<FMT> &ws, WalkState &st, int lane,
+                                                bool flush) {
+  const uint32_t need = flush ? 1u : 32u;
+  while (st.n_label >= need) {
+    const uint32_t take = min(st.n_label, 32u);
+    if (lane < take) prm.label[st.w_label + lane] = ToFloat(txt, ws.q_label[lane], 0);
+    st.w_label += take;
+    QueuePop(ws.q_label, st.n_label, take, lane);
+  }
+  while (st.n_weight >= need) {
+    const uint32_t take = min(st.n_weight, 32u);
+    if (lane < take) prm.weight[st.w_weight + lane] = ToFloat(txt, ws.q_weight[lane], 0);
+    st.w_weight += take;
+    QueuePop(ws.q_weight, st.n_weight, take, lane);
+  }
+  if (FMT == kLibSVM) {
+    while (st.n_qid >= need) {
+      const uint32_t take = min(st.n_qid, 32u);
+      if (lane < take) prm.qid[st.w_qid + lane] = ToQid(txt, ws.q_qid[lane]);
+      st.w_qid += take;
+      QueuePop(ws.q_qid, st.n_qid, take, lane);
+    }
+  }
+  while (st.n_index >= need) {
+    const uint32_t take = min(st.n_index, 32u);
+    bool neg = false;
+    if (lane < take) {
+      StoreIdx<IdxT>(prm.index, st.w_index + lane,
+                     ToUint<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg));
+      if (FMT == kLibFM) {
+        StoreIdx<IdxT>(prm.field, st.w_index + lane,
+                       ToUint<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg));
+      }
+    }
+    if (neg) st.error |= kErrNegativeIndex; /* lane-local; OR-reduced at the end of the walk */
+    st.w_index += take;
+    if (FMT == kLibFM) {
+      uint32_t fill = st.n_index;
+      QueuePop(ws.q_field, fill, take, lane);
+    }
+    QueuePop(ws.q_index, st.n_index, take, lane);
+  }
+  while (st.n_value >= need) {
+    const uint32_t take = min(st.n_value, 32u);
+    if (lane < take) prm.value[st.w_value + lane] = ToFloat(txt, ws.q_value[lane], 0);
+    st.w_value += take;
+    QueuePop(ws.q_value, st.n_value, take, lane);
+  }
+}
+
+/*
+ * One group of <= 32 LibSVM / LibFM tokens (digit runs), one per lane, in file order.
+ * Pairing rules restated from ParsePair / ParseTriple (reference strtonum.h:227-303):
+ * a token is "bound" to the previous one when the separator between them is
+ * [blank]* ':' [anything but digitchars / EOL]*; bound tokens form a chain.  In the first chain
+ * of a line positions 1,2 are label, weight (libsvm_parser.h:50-61); everything after that is
+ * consumed in groups of 2 (index[:value]) or 3 (field:index[:value]).
+ */
+template <int FMT, typename IdxT, bool EMIT>
+__device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &txt,
+                                           WarpScratch<FMT> &ws, WalkState &st, uint32_t head,
+                                           uint32_t count, int lane) {
+  const bool active = lane < count;
+  const uint32_t at = active ? ws.tokens[head + lane] : 0u;
+
+  /* ---- look back over the separator in front of this token ---- */
+  bool line_start = true;   /* separator contains an EOL (or the chunk starts here) */
+  bool bound = false;
+  bool qid_a = false, qid_b = false;     /* separator is [blank]*"qid:"... / [space]*"qid:"... */
+  uint32_t qid_at_a = 0, qid_at_b = 0;   /* byte after that "qid:" */
+  if (active) {
+    const uint32_t kQid = (uint32_t(':') << 24) | (uint32_t('d') << 16) | (uint32_t('i') << 8) |
+                          uint32_t('q');
+    uint32_t first_nonblank = 0, window = 0;
+    bool in_a = false, in_b = false;
+    uint32_t q = at;
+    for (;;) {
+      if (q == 0u) break;               /* start of chunk: a line starts here */
+      --q;
+      const uint32_t c = txt.at(q);
+      if (IsEol(c)) break;
+      if (IsDigitChar(c)) {             /* previous token ends at q */
+        line_start = false;
+        bound = (first_nonblank == ':');
+        if (FMT == kLibSVM) {
+          if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; }
+          if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; }
+        }
+        break;
+      }
+      const bool space = (c == ' ');
+      const bool blank = space || c == '\t';
+      if (!blank) first_nonblank = c;
+      if (FMT == kLibSVM) {
+        /* leading-separator tracking for "qid:" (libsvm_parser.h:66-75): after `label` the
+           reference has skipped blanks, after `label:weight` only spaces */
+        if (blank) {
+          if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; in_a = true; }
+        } else {
+          in_a = false; qid_a = false;
+        }
+        if (space) {
+          if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; in_b = true; }
+        } else {
+          in_b = false; qid_b = false;
+        }
+        window = (window << 8) | c;
+      }
+    }
+  }
+
+  /* ---- chain position and role, by ballot ---- */
+  const uint32_t act_m = __ballot_sync(0xffffffffu, active);
+  const uint32_t nl_m = __ballot_sync(0xffffffffu, active && line_start);
+  const uint32_t bd_m = __ballot_sync(0xffffffffu, active && bound);
+  const uint32_t starts = act_m & ~bd_m;              /* tokens that open a chain */
+  const uint32_t below = starts & LaneMaskLe();
+  int pos;
+  bool first;
+  if (below != 0u) {
+    const int j = 31 - __clz(below);
+    pos = lane - j + 1;
+    first = (nl_m >> j) & 1u;
+  } else {
+    pos = st.carry_pos + lane + 1;
+    first = st.carry_first;
+  }
+  int prev_pos = __shfl_up_sync(0xffffffffu, pos, 1);
+  int prev_first = __shfl_up_sync(0xffffffffu, static_cast<int>(first), 1);
+  uint32_t prev_at = __shfl_up_sync(0xffffffffu, at, 1);
+  if (lane == 0) {
+    prev_pos = st.carry_pos;
+    prev_first = st.carry_first;
+    prev_at = st.carry_at;
+  }
+
+  bool is_label = false, is_weight = false, is_index = false, is_value = false, is_field = false;
+  if (active) {
+    if (first && pos == 1) {
+      is_label = true;
+    } else if (first && pos == 2) {
+      is_weight = true;
+    } else {
+      const int k = first ? pos - 3 : pos - 1;
+      if (FMT == kLibSVM) {
+        is_index = (k & 1) == 0;
+        is_value = !is_index;
+      } else {
+        const int r = k % 3;
+        is_field = r == 0;   /* emitted only if an index follows: done by the index token */
+        is_index = r == 1;
+        is_value = r == 2;
+      }
+    }
+  }
+  bool is_qid = false;
+  if (FMT == kLibSVM) {
+    is_qid = active && !line_start && !bound && prev_first && prev_pos <= 2 &&
+             (prev_pos == 1 ? qid_a : qid_b);
+  }
+
+  const uint32_t lt = LaneMaskLt();
+  const uint32_t m_label = __ballot_sync(0xffffffffu, is_label);
+  const uint32_t m_weight = __ballot_sync(0xffffffffu, is_weight);
+  const uint32_t m_index = __ballot_sync(0xffffffffu, is_index);
+  const uint32_t m_value = __ballot_sync(0xffffffffu, is_value);
+  const uint32_t m_qid = FMT == kLibSVM ? __ballot_sync(0xffffffffu, is_qid) : 0u;
+
+  if (EMIT) {
+    /* row pointer: a label token opens row r; offset[r] = features stored before it
+       (libsvm_parser.h:62-64 push the running index count) */
+    if (is_label) {
+      prm.offset[st.seen[kRows] + __popc(m_label & lt)] =
+          static_cast<unsigned long long>(st.seen[kNnz] + __popc(m_index & lt));
+    }
+    if (FMT == kLibFM && is_field && txt.at(at) == '-') {
+      /* a field id is converted before the reference knows whether the triple is kept
+         (libfm_parser.h:73), so a '-' raises even on a token that is then dropped */
+      st.error |= kErrNegativeIndex;
+    }
+    if (is_label) ws.q_label[st.n_label + __popc(m_label & lt)] = at;
+    if (is_weight) ws.q_weight[st.n_weight + __popc(m_weight & lt)] = at;
+    if (is_index) {
+      const uint32_t slot = st.n_index + __popc(m_index & lt);
+      ws.q_index[slot] = at;
+      if (FMT == kLibFM) ws.q_field[slot] = prev_at;
+    }
+    if (is_value) ws.q_value[st.n_value + __popc(m_value & lt)] = at;
+    if (FMT == kLibSVM && is_qid) {
+      ws.q_qid[st.n_qid + __popc(m_qid & lt)] = (prev_pos == 1) ? qid_at_a : qid_at_b;
+    }
+    st.n_label += __popc(m_label);
+    st.n_weight += __popc(m_weight);
+    st.n_index += __popc(m_index);
+    st.n_value += __popc(m_value);
+    st.n_qid += __popc(m_qid);
+    __syncwarp();
+  }
+  st.seen[kRows] += __popc(m_label);
+  st.seen[kNnz] += __popc(m_index);
+  st.seen[kValues] += __popc(m_value);
+  st.seen[kWeights] += __popc(m_weight);
+  st.seen[kQids] += __popc(m_qid);
+
+  const int last = static_cast<int>(count) - 1;
+  st.carry_pos = __shfl_sync(0xffffffffu, pos, last);
+  st.carry_first = __shfl_sync(0xffffffffu, static_cast<int>(first), last) != 0;
+  st.carry_at = __shfl_sync(0xffffffffu, at, last);
+
+  if (EMIT) DrainRoleQueues<FMT, IdxT>(prm, txt, ws, st, lane, false);
+}
+
+/*
+ * One group of <= 32 CSV fields, one per lane (reference csv_parser.h:73-102).  A queue entry
+ * is the byte position of the field start with bit 31 set when the field opens a row.
+ * Every field is converted with ToFloat; column == label_column goes to label[], every other
+ * column to (index = running column id without the label column, value).
+ */
+template <typename IdxT, bool EMIT>
+__device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &txt,
+                                           WarpScratch<kCSV> &ws, WalkState &st, uint32_t head,
+                                           uint32_t count, int lane) {
+  const bool active = lane < count;
+  const uint32_t entry = active ? ws.tokens[head + lane] : 0u;
+  const bool row_start = active && (entry >> 31) != 0u;
+  const uint32_t at = entry & 0x7fffffffu;
+  const uint32_t rs_m = __ballot_sync(0xffffffffu, row_start);
+  const uint32_t below = rs_m & LaneMaskLe();
+  uint32_t col;
+  if (below != 0u) {
+    col = lane - (31 - __clz(below));
+  } else {
+    col = st.carry_col + lane + 1u;
+  }
+  const bool is_label = active && static_cast<int32_t>(col) == prm.label_column;
+  const bool is_value = active && !is_label;
+  const uint32_t lt = LaneMaskLt();
+  const uint32_t m_value = __ballot_sync(0xffffffffu, is_value);
+  if (EMIT) {
+    const uint32_t row = st.seen[kRows] + __popc(rs_m & LaneMaskLe()) - 1u; /* row of this field */
+    if (row_start) {
+      prm.offset[st.seen[kRows] + __popc(rs_m & lt)] =
+          static_cast<unsigned long long>(st.seen[kNnz] + __popc(m_value & lt));
+    }
+    if (active) {
+      const float v = ToFloat(txt, at, 0);
+      if (is_label) {
+        prm.label[row] = v;
+      } else {
+        const uint32_t slot = st.seen[kNnz] + __popc(m_value & lt);
+        const uint32_t idx =
+            col - ((prm.label_column >= 0 && static_cast<int32_t>(col) > prm.label_column) ? 1u : 0u);
+        prm.value[slot] = v;
+        StoreIdx<IdxT>(prm.index, slot, idx);
+      }
+    }
+  }
+  st.seen[kRows] += __popc(rs_m);
+  st.seen[kNnz] += __popc(m_value);
+  st.seen[kValues] += __popc(m_value);
+  st.carry_col = __shfl_sync(0xffffffffu, col, static_cast<int>(count) - 1);
+}
+
+/*
+ * The walk.  grid = ceil(num_ranges / kWarpsPerCta) CTAs of kCtaThreads; warp w of the grid owns
+ * byte range [w * range_bytes, (w+1) * range_bytes): the lines whose first byte lies in it.
+ */
+template <int FMT, typename IdxT, bool EMIT>
+__global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
+  __shared__ WarpScratch<FMT> scratch[kWarpsPerCta];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t range = blockIdx.x * kWarpsPerCta + warp;
+  if (range >= prm.num_ranges) return;
+  WarpScratch<FMT> &ws = scratch[warp];
+  const Text txt = {prm.text, prm.size};
+
+  if (EMIT) {
+    /* capacity guard: if the arrays cannot hold this chunk nothing is written; the host sees
+       kErrCapacity in the summary, grows the buffers and launches pass 2 again */
+    const ChunkSummary *sum = prm.summary;
+    if (sum->total[kRows] > prm.cap_rows || sum->total[kNnz] > prm.cap_nnz) return;
+    if (range == 0 && lane == 0) prm.offset[sum->total[kRows]] = sum->total[kNnz];
+  }
+
+  const uint32_t lo = range * prm.range_bytes;
+  const uint32_t hi = min(lo + prm.range_bytes, prm.size);
+
+  /* owned bytes [begin, end): begin = first line start at or after lo, end = first line start
+     at or after hi (both "one past an EOL byte"); the same cut the reference makes per OpenMP
+     slice with BackFindEndLine (text_parser.h:71-77,108-116), here looking forward */
+  uint32_t begin = 0;
+  if (range != 0) {
+    const uint32_t e = FindEol(prm.text, prm.size, lo - 1u, hi - 1u, lane);
+    begin = (e == 0xffffffffu) ? hi : e + 1u;
+  }
+
+  WalkState st;
+#pragma unroll
+  for (int c = 0; c < kNumCounters; ++c) st.seen[c] = 0;
+  st.carry_pos = 0;
+  st.carry_first = false;
+  st.carry_at = 0;
+  st.carry_col = 0;
+  st.n_label = st.n_weight = st.n_qid = st.n_index = st.n_value = 0;
+  st.w_label = st.w_weight = st.w_qid = st.w_index = st.w_value = 0;
+  st.error = 0;
+  if (EMIT) {
+#pragma unroll
+    for (int c = 0; c < kNumCounters; ++c) st.seen[c] = prm.counts[c * prm.num_ranges + range];
+    st.w_label = st.seen[kRows];
+    st.w_index = st.seen[kNnz];
+    st.w_value = st.seen[kValues];
+    st.w_weight = st.seen[kWeights];
+    st.w_qid = st.seen[kQids];
+  }
+
+  if (begin < hi) {
+    uint32_t fill = 0;          /* tokens waiting in ws.tokens */
+    uint32_t end = prm.size;    /* tightened once the closing EOL is seen */
+    uint32_t prev_a = 0;        /* LibSVM/LibFM: last byte of previous lane/step was in a run.
+                                   CSV: last byte was a comma */
+    uint32_t prev_eol = 1;      /* CSV: last byte was an EOL (a line starts at `begin`) */
+    bool done = false;
+    for (uint32_t base = begin & ~uint32_t(kStepBytes - 1); !done; base += kStepBytes) {
+      const uint32_t first_byte = base + 16u * lane;
+      const uint4 v = Load16(prm.text, prm.size, first_byte);
+      const Masks16 raw = Classify<FMT>(v); /* bytes past the chunk load as NUL: no class */
+      /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
+      {
+        const uint32_t closing = raw.eol & KeepMask(first_byte, hi - 1u, prm.size);
+        const uint32_t who = __ballot_sync(0xffffffffu, closing != 0u);
+        if (who != 0u) {
+          const int src = __ffs(who) - 1;
+          const uint32_t es = __shfl_sync(0xffffffffu, closing, src);
+          end = base + 16u * src + (__ffs(es) - 1) + 1u;
+          done = true;
+        } else if (base + kStepBytes >= prm.size) {
+          done = true;
+        }
+      }
+      const uint32_t keep = KeepMask(first_byte, begin, end);
+
+      /* token starts in this lane's 16 bytes */
+      uint32_t starts, row_starts = 0;
+      if (FMT == kCSV) {
+        /* a field starts after a comma or at a line start, unless that byte is an EOL
+           (csv_parser.h:79-95: a trailing comma yields no extra column).  The raw masks are
+           used for "what precedes me" so that the line start at `begin` is seen. */
+        uint32_t up_c = __shfl_up_sync(0xffffffffu, raw.a >> 15, 1);
+        uint32_t up_e = __shfl_up_sync(0xffffffffu, raw.eol >> 15, 1);
+        if (lane == 0) {
+          up_c = prev_a;
+          up_e = prev_eol;
+        }
+        const uint32_t after_comma = ((raw.a << 1) | up_c) & 0xffffu;
+        const uint32_t after_eol = ((raw.eol << 1) | up_e) & 0xffffu;
+        row_starts = after_eol & ~raw.eol & keep;
+        starts = (after_comma | after_eol) & ~raw.eol & keep;
+        prev_a = __shfl_sync(0xffffffffu, raw.a >> 15, 31);
+        prev_eol = __shfl_sync(0xffffffffu, raw.eol >> 15, 31);
+      } else {
+        /* a digit run cannot cross `begin` or `end` (both follow an EOL byte) */
+        const uint32_t runs = raw.a & keep;
+        uint32_t up_a = __shfl_up_sync(0xffffffffu, runs >> 15, 1);
+        if (lane == 0) up_a = prev_a;
+        starts = runs & ~((runs << 1) | up_a);
+        prev_a = __shfl_sync(0xffffffffu, runs >> 15, 31);
+      }
+      /* compact them, in file order, behind the tokens left from the previous step */
+      {
+        const uint32_t mine = __popc(starts);
+        const uint32_t incl = WarpInclusiveSum(mine, lane);
+        uint32_t slot = fill + incl - mine;
+        uint32_t bits = starts;
+        while (bits != 0u) {
+          const uint32_t b = __ffs(bits) - 1;
+          bits &= bits - 1u;
+          uint32_t entry = first_byte + b;
+          if (FMT == kCSV) entry |= ((row_starts >> b) & 1u) << 31;
+          ws.tokens[slot++] = entry;
+        }
+        fill += __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();
+      }
+      /* handle full groups (all of them when the region is finished) */
+      uint32_t head = 0;
+      while (fill - head >= 32u || (done && fill > head)) {
+        const uint32_t count = min(fill - head, 32u);
+        if constexpr (FMT == kCSV) {
+          FieldGroup<IdxT, EMIT>(prm, txt, ws, st, head, count, lane);
+        } else {
+          TokenGroup<FMT, IdxT, EMIT>(prm, txt, ws, st, head, count, lane);
+        }
+        head += count;
+      }
+      /* move the < 32 left-over tokens to the front */
+      if (head != 0u) {
+        const uint32_t rest = fill - head;
+        uint32_t moved = 0;
+        if (lane < rest) moved = ws.tokens[head + lane];
+        __syncwarp();
+        if (lane < rest) ws.tokens[lane] = moved;
+        __syncwarp();
+        fill = rest;
+      }
+    }
+    if constexpr (EMIT && FMT != kCSV) DrainRoleQueues<FMT, IdxT>(prm, txt, ws, st, lane, true);
+  }
+
+  if (EMIT) {
+    const uint32_t err = __reduce_or_sync(0xffffffffu, st.error);
+    if (err != 0u && lane == 0) atomicOr(&prm.summary->error, err);
+  } else {
+    if (lane < kNumCounters) {
+      uint32_t v = 0;
+#pragma unroll
+      for (int c = 0; c < kNumCounters; ++c) v = (lane == c) ? st.seen[c] : v;
+      prm.counts[lane * prm.num_ranges + range] = v;
+    }
+  }
+}
+
+/*
+ * Exclusive prefix sums of the per-range counters, in place, plus the chunk totals and the
+ * RowBlock consistency check of the reference (row_block.h:177).  One CTA: the counter arrays
+ * are tiny (5 x chunk_bytes / range_bytes words).
+ */
+__global__ void __launch_bounds__(1024) ScanRanges(uint32_t *counts, uint32_t num_ranges,
+                                                   ChunkSummary *summary) {
+  __shared__ uint32_t partial[kNumCounters][1024];
+  const uint32_t tid = threadIdx.x;
+  const uint32_t per = (num_ranges + 1023u) / 1024u;
+  const uint32_t lo = min(tid * per, num_ranges);
+  const uint32_t hi = min(lo + per, num_ranges);
+  uint32_t sum[kNumCounters];
+#pragma unroll
+  for (int c = 0; c < kNumCounters; ++c) {
+    uint32_t s = 0;
+    for (uint32_t i = lo; i < hi; ++i) s += counts[c * num_ranges + i];
+    sum[c] = s;
+    partial[c][tid] = s;
+  }
+  __syncthreads();
+  /* Hillis-Steele inclusive scan across the 1024 partials of each counter */
+  for (uint32_t d = 1; d < 1024u; d <<= 1) {
+    uint32_t add[kNumCounters];
+#pragma unroll
+    for (int c = 0; c < kNumCounters; ++c) add[c] = tid >= d ? partial[c][tid - d] : 0u;
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < kNumCounters; ++c) partial[c][tid] += add[c];
+    __syncthreads();
+  }
+#pragma unroll
+  for (int c = 0; c < kNumCounters; ++c) {
+    uint32_t run = partial[c][tid] - sum[c];
+    for (uint32_t i = lo; i < hi; ++i) {
+      const uint32_t v = counts[c * num_ranges + i];
+      counts[c * num_ranges + i] = run;
+      run += v;
+    }
+  }
+  if (tid == 1023u) {
+    unsigned int err = 0;
+#pragma unroll
+    for (int c = 0; c < kNumCounters; ++c) summary->total[c] = partial[c][1023];
+    if (partial[kValues][1023] != 0u && partial[kValues][1023] != partial[kNnz][1023]) {
+      err |= kErrValueCount;
+    }
+    summary->error = err;
+    summary->ranges = num_ranges;
+  }
+}
+
+}  // namespace b200p
+#endif  // DMLC_CORE_B200_TEXT_KERNELS_CUH_

@@ -1,0 +1,141 @@
+/*
+ * dmlc_b200_parser.h -- C ABI of the B200 text -> CSR parser (libdmlc_b200.so).
+ *
+ * This is the whole boundary between a host program (the dmlc::Parser<IndexType> shim in
+ * dmlc_core_b200/src, a ctypes binding, cgo, JNI ...) and the sm_100a kernels: plain pointers
+ * and sizes, no C++ or torch types.  Each entry point names the reference interface it stands
+ * in for (paths relative to rahul003/dmlc-core).
+ *
+ * Threading: a handle is single-consumer, like a dmlc::Parser instance
+ * (reference include/dmlc/data.h:283-311). Distinct handles (e.g. one per GPU / part_index) are
+ * independent.
+ *
+ * Return values: 0 = success; B200P_E_* otherwise. After a failure b200p_last_error(handle)
+ * describes it. B200P_E_PARSE is the data error the reference raises as dmlc::Error
+ * (negative unsigned field: src/data/strtonum.h:141; value/index count mismatch:
+ * src/data/row_block.h:177) -- the C++ layer turns it back into `throw dmlc::Error`.
+ */
+#ifndef DMLC_B200_PARSER_H_
+#define DMLC_B200_PARSER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200P_OK 0
+#define B200P_E_INVALID 1   /* bad argument / call sequence */
+#define B200P_E_CUDA 2      /* CUDA runtime failure (no usable GPU, out of memory ...) */
+#define B200P_E_PARSE 3     /* input makes the reference parser throw dmlc::Error */
+#define B200P_E_AGAIN 4     /* no free pipeline slot: call b200p_next first */
+#define B200P_E_EMPTY 5     /* nothing submitted */
+
+#define B200P_FORMAT_LIBSVM 0 /* src/data/libsvm_parser.h */
+#define B200P_FORMAT_LIBFM 1  /* src/data/libfm_parser.h */
+#define B200P_FORMAT_CSV 2    /* src/data/csv_parser.h */
+
+/* largest chunk one call may carry (token positions are 31-bit on the device) */
+#define B200P_MAX_CHUNK_BYTES ((uint64_t)1 << 30)
+
+typedef struct b200p_parser_s *b200p_handle;
+
+/*
+ * Parser configuration.  Stands in for the constructor arguments of
+ * LibSVMParser / LibFMParser / CSVParser (src/data/libsvm_parser.h:24-27,
+ * src/data/csv_parser.h:43-52) plus the template IndexType of dmlc::Parser.
+ */
+typedef struct b200p_config {
+  int32_t format;        /* B200P_FORMAT_* */
+  int32_t index_bytes;   /* sizeof(IndexType): 4 or 8 */
+  int32_t label_column;  /* CSVParserParam::label_column (csv_parser.h:24,31), -1 = none */
+  int32_t device;        /* CUDA device ordinal */
+  uint64_t chunk_bytes;  /* expected chunk size, sizes the staging buffers (0 = 64 MiB) */
+  int32_t range_bytes;   /* bytes of text one warp owns (0 = default); tuning only */
+  int32_t depth;         /* chunks in flight for b200p_submit/b200p_next (0 = 3) */
+  void *stream;          /* cudaStream_t for the device-resident calls; NULL = own stream */
+} b200p_config;
+
+/*
+ * One parsed chunk.  Field for field the RowBlock<IndexType> of include/dmlc/data.h:169-231
+ * (size, offset, label, weight, qid, field, index, value), plus the true lengths of the
+ * optional arrays, which the reference hides behind raw pointers.  Arrays that stayed empty
+ * are NULL, as RowBlockContainer::GetBlock does with BeginPtr (src/data/row_block.h:180-186).
+ * offset[0] == 0; offset has rows + 1 entries.
+ */
+typedef struct b200p_rowblock {
+  uint64_t rows;       /* RowBlock::size */
+  uint64_t nnz;        /* offset[rows] */
+  uint64_t n_weight;   /* entries in weight (0 or, for well-formed input, rows) */
+  uint64_t n_qid;
+  uint64_t n_field;    /* 0 or nnz */
+  uint64_t n_value;    /* 0 or nnz */
+  const uint64_t *offset;
+  const float *label;
+  const float *weight;
+  const uint64_t *qid;
+  const void *field;   /* index_bytes wide */
+  const void *index;   /* index_bytes wide */
+  const float *value;
+  uint64_t text_bytes; /* size of the chunk this block came from (-> Parser::BytesRead) */
+  int32_t index_bytes;
+  int32_t on_device;   /* 1: pointers are device memory, 0: pinned host memory */
+} b200p_rowblock;
+
+/* Replaces: new LibSVMParser<I>(source, nthread) etc. (src/data.cc:21-60). Allocates the
+   device-side staging; fails with B200P_E_CUDA when there is no GPU -- there is no CPU path. */
+int b200p_create(const b200p_config *config, b200p_handle *out);
+
+/* Replaces: delete parser (src/data/text_parser.h:37-39). */
+void b200p_destroy(b200p_handle h);
+
+/* Text of the last failure on this handle ("" if none). h may be NULL for create failures. */
+const char *b200p_last_error(b200p_handle h);
+
+/*
+ * Device-resident parse: the chunk already sits in HBM (16-byte aligned, nbytes <=
+ * B200P_MAX_CHUNK_BYTES, cut after an end-of-line byte unless it is the last of its stream) and
+ * the CSR arrays stay in HBM (out->on_device == 1, valid until the next call on this handle).
+ * Replaces: TextParserBase::FillData + ParseBlock on one chunk (src/data/text_parser.h:93-134).
+ * b200p_parse_device = b200p_parse_device_async + b200p_parse_device_finish.
+ * The async half only enqueues the kernels on the handle's stream and never synchronises.
+ */
+int b200p_parse_device(b200p_handle h, const void *d_text, uint64_t nbytes, b200p_rowblock *out);
+int b200p_parse_device_async(b200p_handle h, const void *d_text, uint64_t nbytes);
+int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out);
+
+/*
+ * Streaming parse from host memory: H2D copy, kernels and D2H copy of chunk k overlap with
+ * those of chunks k+1.. on separate streams (the GPU-side counterpart of the reference's two
+ * prefetch stages, src/io/threaded_input_split.h:29-42 and src/data/parser.h:73-82).
+ *
+ *   b200p_input_buffer  pinned staging buffer of the next free slot, to be filled in place
+ *                       (e.g. by pread); capacity >= config.chunk_bytes.
+ *   b200p_submit        enqueue a chunk. `text` may be the pointer b200p_input_buffer returned
+ *                       (zero-copy) or any host memory (copied into the staging buffer first).
+ *   b200p_next          wait for the oldest submitted chunk; pointers are pinned host memory,
+ *                       valid until the next b200p_next / b200p_destroy on this handle.
+ * Replaces: ParserImpl::ParseNext -> FillData (src/data/parser.h:30-44, text_parser.h:93-134).
+ */
+int b200p_input_buffer(b200p_handle h, void **host_ptr, uint64_t *capacity);
+int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes);
+int b200p_next(b200p_handle h, b200p_rowblock *out);
+/* chunks submitted and not yet returned by b200p_next */
+int b200p_pending(b200p_handle h);
+
+/* Copy nbytes from device memory returned by the device-resident calls into host memory,
+   ordered after the handle's stream (for callers that do not link the CUDA runtime).
+   No reference counterpart: the reference never leaves host memory. */
+int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t nbytes);
+
+/* number of kernels this handle has launched so far (bench.py's gpu_launches claim) */
+uint64_t b200p_launch_count(b200p_handle h);
+
+/* library / build identification: "dmlc_b200 <version> sm_100a" */
+const char *b200p_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DMLC_B200_PARSER_H_ */

@@ -1,0 +1,208 @@
+"""GPU parity suite (-m gpu): the CUDA path, called through the C ABI, against the oracle
+(oracle/dmlc_oracle.c) and the committed golden RowBlocks of the unmodified reference.
+Bit-exact for every array; floats are compared as IEEE bit patterns (tolerance: 0 ulp)."""
+import random
+
+import numpy as np
+import pytest
+
+from conftest import golden_cases, load_golden
+from oracle.pyoracle import same_rowblocks
+
+pytestmark = pytest.mark.gpu
+
+
+def _parser(cuda_lib, fmt, ib=4, lc=-1, **kw):
+    from dmlc_core_b200 import Parser
+    return Parser(fmt, index_bytes=ib, label_column=lc, **kw)
+
+
+def _gpu_result(parser, text, path):
+    from dmlc_core_b200 import ParseError
+    from gpu_util import parse_on_device
+    try:
+        if path == "device":
+            return parse_on_device(parser, text)
+        return parser.parse_host(text)
+    except ParseError as e:
+        return {"error": 1, "errmsg": str(e)}
+
+
+@pytest.mark.parametrize("path", ["device", "host"])
+@pytest.mark.parametrize("case", golden_cases(), ids=lambda c: c["name"])
+def test_golden(cuda_lib, case, path):
+    text, exp = load_golden(case)
+    for rb in (512, 0):
+        p = _parser(cuda_lib, case["format"], case["index_bytes"], case["label_column"], range_bytes=rb)
+        got = _gpu_result(p, text, path)
+        p.close()
+        assert same_rowblocks(got, exp) is None, (case["name"], rb)
+
+
+def _random_text(rnd, nlines):
+    def num():
+        k = rnd.random()
+        if k < 0.3:
+            return str(rnd.randint(0, 10 ** rnd.randint(1, 12)))
+        if k < 0.6:
+            return "%.6g" % rnd.uniform(-100, 100)
+        if k < 0.7:
+            return "%e" % rnd.uniform(-1e10, 1e10)
+        if k < 0.8:
+            return rnd.choice(["+1", "1", ".5", "1.", "e", "1e5e3", "1-2", "+", "007"])
+        return "".join(rnd.choice("0123456789.eE+") for _ in range(rnd.randint(1, 8)))
+    seps = [" ", " ", " ", "  ", "\t", ":", ":", " : ", ": ", " :", ",", "|", "qid:", " qid:", "x", "::"]
+    eols = ["\n", "\n", "\n", "\r\n", "\r", "\n\n"]
+    out = []
+    for _ in range(nlines):
+        line = "".join(num() + rnd.choice(seps) for _ in range(rnd.randint(0, 14)))
+        out.append(line + rnd.choice(eols))
+    return "".join(out).encode()
+
+
+@pytest.mark.parametrize("fmt,ib", [("libsvm", 4), ("libsvm", 8), ("libfm", 4), ("libfm", 8), ("csv", 4)])
+def test_adversarial_fuzz(cuda_lib, oracle, fmt, ib):
+    """Random separators / odd tokens / CRLF / qid / chains, small and multi-range inputs.
+    The trailing-colon-at-end-of-line form is excluded: the reference reads past the line there
+    (declared malformed); every other quirk must match, including which inputs throw."""
+    rnd = random.Random(1234 + ib + len(fmt))
+    lc = 1 if fmt == "csv" else -1
+    parsers = [_parser(cuda_lib, fmt, ib, lc, range_bytes=rb) for rb in (512, 1024, 0)]
+    done = 0
+    while done < 500:
+        text = _random_text(rnd, rnd.choice([1, 3, 10, 60, 300]))
+        bad = False
+        for line in text.replace(b"\r", b"\n").split(b"\n"):
+            s = line.rstrip(b" \t|x,")
+            if fmt != "csv" and (s.endswith(b":") or line.rstrip(b" \t").endswith(b":") or
+                                 line.endswith(b"qid:") or line.endswith(b"::")):
+                bad = True
+            if fmt == "csv" and line != line.rstrip(b" \t"):
+                bad = True  # whitespace before EOL: reference strtof runs into the next line
+        if bad or b":\n" in text or b":\r" in text:
+            continue
+        done += 1
+        exp = oracle.parse_buffer(fmt, text, ib, lc)
+        for p in parsers:
+            got = _gpu_result(p, text, "device")
+            assert same_rowblocks(got, exp) is None, (fmt, ib, text)
+    for p in parsers:
+        p.close()
+
+
+CORPORA = [("libsvm", "libsvm", 4, -1), ("csv", "csv", 4, 0), ("libfm", "libfm", 8, -1),
+           ("libsvm_qid", "libsvm", 4, -1), ("criteo", "libsvm", 8, -1), ("libfm", "libfm", 4, -1)]
+
+
+@pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA)
+def test_corpus_device(cuda_lib, oracle, kind, fmt, ib, lc):
+    """The five BASELINE.json corpus shapes, a few MB each, at several range sizes."""
+    from dmlc_core_b200 import datagen
+    data, rows = datagen.generate(kind, 5, 3 << 20)
+    exp = oracle.parse_buffer(fmt, data.tobytes(), ib, lc)
+    assert exp["error"] == 0 and len(exp["label"]) == rows
+    for rb in (512, 1536, 8192, 65536):
+        p = _parser(cuda_lib, fmt, ib, lc, range_bytes=rb)
+        got = _gpu_result(p, data, "device")
+        again = _gpu_result(p, data, "device")   # same handle, second chunk: provisioned path
+        p.close()
+        assert same_rowblocks(got, exp) is None, (kind, rb)
+        assert same_rowblocks(again, exp) is None, (kind, rb)
+
+
+@pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA[:4])
+def test_corpus_streaming(cuda_lib, oracle, kind, fmt, ib, lc):
+    """b200p_submit / b200p_next with several chunks in flight; chunks cut at line ends.
+    The concatenation over chunks equals the oracle on the whole text (SURVEY 8a contract)."""
+    from dmlc_core_b200 import datagen
+    data, rows = datagen.generate(kind, 6, 6 << 20)
+    raw = data.tobytes()
+    exp = oracle.parse_buffer(fmt, raw, ib, lc)
+    cuts, pos, rnd = [0], 0, random.Random(3)
+    while pos < len(raw):
+        pos = min(len(raw), pos + rnd.randint(100 << 10, 900 << 10))
+        if pos < len(raw):
+            pos = raw.index(b"\n", pos) + 1
+        cuts.append(pos)
+    p = _parser(cuda_lib, fmt, ib, lc, chunk_bytes=1 << 20, depth=3)
+    blocks, i = [], 0
+    chunks = [raw[a:b] for a, b in zip(cuts[:-1], cuts[1:])]
+    for c in chunks:
+        while p.pending() >= 3:
+            blocks.append(p.next())
+        p.submit(c)
+    while p.pending():
+        blocks.append(p.next())
+    p.close()
+    assert len(blocks) == len(chunks)
+    got = {k: np.concatenate([b[k] for b in blocks]) for k in ("label", "weight", "qid", "field", "index", "value")}
+    offs, run = [np.zeros(1, dtype=np.uint64)], 0
+    for b in blocks:
+        offs.append(b["offset"][1:] + np.uint64(run))
+        run += len(b["index"])
+    got["offset"] = np.concatenate(offs)
+    got["error"] = 0
+    assert same_rowblocks(got, exp) is None
+
+
+def test_edge_inputs(cuda_lib, oracle):
+    cases = [
+        ("libsvm", b""), ("libsvm", b"\n"), ("libsvm", b"\n\n\r\n"), ("libsvm", b"1"), ("libsvm", b"1 2:3"),
+        ("libsvm", b"1 2:3\n0 4:5"), ("libsvm", b"   \n1 1:1\n"), ("csv", b""), ("csv", b"\n\n"),
+        ("csv", b"1,2"), ("csv", b"1,2\n3,4"), ("csv", b","), ("csv", b",,,\n"), ("libfm", b"1 1:2:3"),
+        # one line far longer than a range, then short ones
+        ("libsvm", b"1 " + b" ".join(b"%d:%d.5" % (i, i) for i in range(1, 4000)) + b"\n0 1:2\n1 3:4\n"),
+        ("csv", b",".join(b"%d.25" % i for i in range(6000)) + b"\n1,2,3\n"),
+        ("libfm", b"0 " + b" ".join(b"%d:%d:1" % (i % 30, i) for i in range(3000)) + b"\n"),
+        # dense value-less tokens: nnz ~ bytes / 2, overflows the first provision -> regrow path
+        ("libsvm", (b"1 " + b"7 " * 4000 + b"\n") * 20),
+    ]
+    for fmt, text in cases:
+        exp = oracle.parse_buffer(fmt, text, 4, 0 if fmt == "csv" else -1)
+        for rb in (512, 0):
+            p = _parser(cuda_lib, fmt, 4, 0 if fmt == "csv" else -1, range_bytes=rb)
+            assert same_rowblocks(_gpu_result(p, text, "device"), exp) is None, (fmt, text[:40], rb)
+            assert same_rowblocks(_gpu_result(p, text, "host"), exp) is None, (fmt, text[:40], rb)
+            p.close()
+
+
+def test_errors_are_reported_like_the_reference(cuda_lib):
+    """Inputs that make the reference throw dmlc::Error give B200P_E_PARSE (-> ParseError)."""
+    from dmlc_core_b200 import ParseError
+    from gpu_util import parse_on_device
+    for fmt, text in (("libsvm", b"1 2:1 -3:0.5\n"), ("libsvm", b"1:0.5 qid:5 1:0.5 3:1.25\n"),
+                      ("libsvm", b"1 3:1 5\n"), ("libfm", b"1 -5 1:2:3\n"), ("libfm", b"1 0:1:0.5 2:3\n")):
+        p = _parser(cuda_lib, fmt)
+        with pytest.raises(ParseError):
+            parse_on_device(p, text)
+        # the handle stays usable afterwards
+        ok = parse_on_device(p, b"1 1:2:3\n" if fmt == "libfm" else b"1 1:2\n")
+        assert len(ok["label"]) == 1
+        p.close()
+
+
+def test_full_size_properties(cuda_lib, oracle):
+    """Size-independent checks at the bench's chunk size (1 GiB of dense CSV, device-resident):
+    tiling a block k times must give k copies of that block's rows (offsets shifted by nnz)."""
+    import torch
+    from dmlc_core_b200 import datagen
+    from gpu_util import as_torch
+    base, rows = datagen.generate("csv", 1, 32 << 20)
+    k = (1 << 30) // base.size
+    big = torch.from_numpy(base).cuda().repeat(k)
+    p = _parser(cuda_lib, "csv", 4, 0)
+    blk = p.parse_device(big.data_ptr(), big.numel())
+    assert blk.rows == rows * k and blk.nnz == rows * k * 128 and blk.n_value == blk.nnz
+    value = as_torch(blk.value, blk.nnz, np.float32).view(k, -1)
+    index = as_torch(blk.index, blk.nnz, np.uint32).view(k, -1)
+    label = as_torch(blk.label, blk.rows, np.float32).view(k, -1)
+    offset = as_torch(blk.offset, blk.rows + 1, np.uint64)
+    assert bool((value == value[0:1]).all()) and bool((index == index[0:1]).all())
+    assert bool((label == label[0:1]).all())
+    assert bool((offset == torch.arange(blk.rows + 1, device="cuda", dtype=torch.int64) * 128).all())
+    # and the first copy is the oracle's answer on one block
+    small = oracle.parse_buffer("csv", base.tobytes(), 4, 0)
+    assert np.array_equal(value[0].cpu().numpy().view(np.uint32), small["value"].view(np.uint32))
+    assert np.array_equal(label[0].cpu().numpy().view(np.uint32), small["label"].view(np.uint32))
+    assert np.array_equal(index[0].cpu().numpy().view(np.uint32), small["index"])
+    p.close()

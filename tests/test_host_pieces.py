@@ -1,0 +1,104 @@
+"""CPU suite: the kernels' token-conversion code compiled for the host, the generators, and the
+C ABI library's loadability / exported symbols (no compute without a GPU)."""
+import ctypes as C
+import os
+import random
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+@pytest.fixture(scope="module")
+def emul():
+    from dmlc_core_b200 import build
+    lib = C.CDLL(build.build_emul())
+    lib.emul_strtof_bits.restype = C.c_uint32
+    lib.emul_strtof_bits.argtypes = [C.c_char_p, C.POINTER(C.c_int64)]
+    lib.emul_strtouint.restype = C.c_uint64
+    lib.emul_strtouint.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int)]
+    lib.emul_atoll.restype = C.c_int64
+    lib.emul_atoll.argtypes = [C.c_char_p]
+    return lib
+
+
+def test_device_token_code_matches_oracle(emul, oracle):
+    rnd = random.Random(21)
+    toks = ["0." + "0" * 64, "-0." + "0" * 70 + "e2", "1e39", "56018346692", "-", "e", ""]
+    for _ in range(100000):
+        toks.append("".join(rnd.choice("0123456789" * 3 + "+-.eE") for _ in range(rnd.randint(1, 26))))
+    for t in toks:
+        n = C.c_int64()
+        got = (emul.emul_strtof_bits(t.encode(), C.byref(n)), n.value)
+        assert got == oracle.strtof_bits(t), t
+    for _ in range(50000):
+        t = "".join(rnd.choice("0123456789" * 4 + "+-. ") for _ in range(rnd.randint(0, 24)))
+        for w in (4, 8):
+            th = C.c_int()
+            v = emul.emul_strtouint(t.encode(), w, C.byref(th))
+            ov, othrew = oracle.strtouint(t, w)
+            assert bool(th.value) == othrew and (othrew or v == ov), (t, w)
+        assert emul.emul_atoll(t.encode()) == oracle.atoll(t), t
+
+
+def test_digitchar_class(emul):
+    want = set(b"0123456789+-.eE")
+    for c in range(256):
+        assert bool(emul.emul_is_digitchar(c)) == (c in want), c
+
+
+def test_generators_are_deterministic_and_wellformed(oracle):
+    from dmlc_core_b200 import datagen
+    for kind, fmt, w, lc in (("libsvm", "libsvm", 4, -1), ("csv", "csv", 4, 0), ("libfm", "libfm", 8, -1),
+                             ("libsvm_qid", "libsvm", 4, -1), ("criteo", "libsvm", 8, -1)):
+        a, rows = datagen.generate(kind, 7, 300 << 10)
+        b, _ = datagen.generate(kind, 7, 300 << 10)
+        assert a.tobytes() == b.tobytes()
+        assert a[-1] == 10
+        res = oracle.parse_buffer(fmt, a.tobytes(), w, lc)
+        assert res["error"] == 0 and len(res["label"]) == rows
+        if kind == "libsvm_qid":
+            assert len(res["qid"]) == rows and len(res["weight"]) == rows and len(res["value"]) == 0
+            assert np.all(np.diff(res["qid"].astype(np.int64)) >= 0)
+        if kind == "csv":
+            assert len(res["index"]) == rows * 128
+
+
+def test_c_abi_library_exports_header_symbols():
+    """libdmlc_b200.so loads without a GPU and exports everything include/*.h declares."""
+    from dmlc_core_b200 import build, capi
+    build.build_cuda()
+    lib = capi.load()
+    with open(os.path.join(ROOT, "include", "dmlc_b200_parser.h")) as f:
+        header = f.read()
+    declared = set(re.findall(r"\b(b200p_[a-z_0-9]+)\s*\(", header))
+    assert declared, "no declarations found"
+    assert declared == set(capi.EXPORTS)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert b"sm_100a" in lib.b200p_version()
+
+
+def test_no_gpu_means_loud_failure():
+    """Without a CUDA device the product refuses to run (no CPU fallback)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from dmlc_core_b200 import Parser
+    with pytest.raises(RuntimeError):
+        Parser("libsvm")
+
+
+def test_product_never_imports_oracle():
+    """The oracle is test infrastructure: nothing under dmlc_core_b200/ may reference it."""
+    pkg = os.path.join(ROOT, "dmlc_core_b200")
+    for base, _, files in os.walk(pkg):
+        for f in files:
+            if f == "build.py":
+                continue  # building the checker is not using it
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cc", ".c")):
+                with open(os.path.join(base, f), errors="replace") as fh:
+                    src = fh.read()
+                assert "pyoracle" not in src and "liboracle" not in src and "libdmlc_ref" not in src, f
