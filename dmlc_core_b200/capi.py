@@ -22,7 +22,7 @@ EXPORTS = (
     "b200p_create", "b200p_destroy", "b200p_last_error", "b200p_parse_device",
     "b200p_parse_device_async", "b200p_parse_device_finish", "b200p_input_buffer",
     "b200p_submit", "b200p_next", "b200p_pending", "b200p_fetch", "b200p_launch_count",
-    "b200p_version",
+    "b200p_set_profiling", "b200p_kernel_time", "b200p_version",
 )
 
 
@@ -82,6 +82,10 @@ def load():
     lib.b200p_fetch.restype = C.c_int
     lib.b200p_launch_count.argtypes = [H]
     lib.b200p_launch_count.restype = C.c_uint64
+    lib.b200p_set_profiling.argtypes = [H, C.c_int]
+    lib.b200p_set_profiling.restype = C.c_int
+    lib.b200p_kernel_time.argtypes = [H, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+    lib.b200p_kernel_time.restype = C.c_int
     lib.b200p_version.argtypes = []
     lib.b200p_version.restype = C.c_char_p
     _lib = lib
@@ -216,6 +220,15 @@ class Parser(object):
 
     def pending(self):
         return int(self.lib.b200p_pending(self.handle))
+
+    def set_profiling(self, on):
+        self._check(self.lib.b200p_set_profiling(self.handle, 1 if on else 0))
+
+    def kernel_time(self, kernel):
+        """(total_ms, launches) of kernel 0=count, 1=scan, 2=emit since profiling was enabled."""
+        ms, n = C.c_double(0), C.c_uint64(0)
+        self._check(self.lib.b200p_kernel_time(self.handle, kernel, C.byref(ms), C.byref(n)))
+        return float(ms.value), int(n.value)
 
     def launch_count(self):
         return int(self.lib.b200p_launch_count(self.handle))

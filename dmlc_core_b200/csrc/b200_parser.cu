@@ -77,6 +77,12 @@ struct b200p_parser_s {
   int returned_slot;         /* slot whose host arrays the caller currently holds, or -1 */
   double rows_per_byte, nnz_per_byte; /* densest chunk seen so far: sizes later allocations */
   uint64_t launches;
+  /* optional per-kernel timing (b200p_set_profiling): event pairs around each launch */
+  bool profiling;
+  struct Timed { int kind; cudaEvent_t start, stop; };
+  std::vector<Timed> timed;
+  double kernel_ms[3];
+  uint64_t kernel_launches[3];
   std::string error;
 };
 
@@ -93,6 +99,34 @@ static thread_local std::string g_create_error;
       return B200P_E_CUDA;                                                             \
     }                                                                                  \
   } while (0)
+
+/* profiling brackets: only active after b200p_set_profiling(h, 1) */
+static void ProfBegin(b200p_handle h, int kind, cudaStream_t s) {
+  if (!h->profiling) return;
+  b200p_parser_s::Timed t;
+  t.kind = kind;
+  cudaEventCreate(&t.start);
+  cudaEventCreate(&t.stop);
+  cudaEventRecord(t.start, s);
+  h->timed.push_back(t);
+}
+static void ProfEnd(b200p_handle h, cudaStream_t s) {
+  if (!h->profiling) return;
+  cudaEventRecord(h->timed.back().stop, s);
+}
+static void ProfCollect(b200p_handle h) {
+  for (size_t i = 0; i < h->timed.size(); ++i) {
+    float ms = 0.f;
+    if (cudaEventSynchronize(h->timed[i].stop) == cudaSuccess &&
+        cudaEventElapsedTime(&ms, h->timed[i].start, h->timed[i].stop) == cudaSuccess) {
+      h->kernel_ms[h->timed[i].kind] += ms;
+      h->kernel_launches[h->timed[i].kind] += 1;
+    }
+    cudaEventDestroy(h->timed[i].start);
+    cudaEventDestroy(h->timed[i].stop);
+  }
+  h->timed.clear();
+}
 
 static int Fail(b200p_handle h, int code, const char *msg) {
   h->error = msg;
@@ -220,7 +254,9 @@ static int EnqueueEmit(b200p_handle h, Slot *s) {
     ZeroLabels<<<296, 256, 0, s->stream>>>(s->dev.label, s->d_summary, s->dev.cap_rows);
     ++h->launches;
   }
+  ProfBegin(h, B200P_KERNEL_EMIT, s->stream);
   LaunchWalk(h, p, s->stream, true);
+  ProfEnd(h, s->stream);
   ++h->launches;
   CUDA_TRY(h, cudaGetLastError());
   CUDA_TRY(h, cudaMemcpyAsync(s->h_summary, s->d_summary, sizeof(ChunkSummary),
@@ -252,8 +288,12 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
     if (rc != B200P_OK) return rc;
   }
   const WalkParams p = MakeParams(h, *s);
+  ProfBegin(h, B200P_KERNEL_COUNT, s->stream);
   LaunchWalk(h, p, s->stream, false);
+  ProfEnd(h, s->stream);
+  ProfBegin(h, B200P_KERNEL_SCAN, s->stream);
   ScanRanges<<<1, 1024, 0, s->stream>>>(s->d_counts, p.num_ranges, s->d_summary);
+  ProfEnd(h, s->stream);
   h->launches += 2;
   CUDA_TRY(h, cudaGetLastError());
   return EnqueueEmit(h, s);
@@ -366,6 +406,8 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->resident_pending = false;
   h->rows_per_byte = h->nnz_per_byte = 0.0;
   h->launches = 0;
+  h->profiling = false;
+  for (int k = 0; k < 3; ++k) { h->kernel_ms[k] = 0.0; h->kernel_launches[k] = 0; }
 
   int count = 0;
   cudaError_t e = cudaGetDeviceCount(&count);
@@ -399,12 +441,30 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
 void b200p_destroy(b200p_handle h) {
   if (h == NULL) return;
   cudaSetDevice(h->cfg.device);
+  ProfCollect(h);
   for (size_t i = 0; i < h->slots.size(); ++i) DestroySlot(&h->slots[i]);
   DestroySlot(&h->resident);
   delete h;
 }
 
 uint64_t b200p_launch_count(b200p_handle h) { return h != NULL ? h->launches : 0; }
+
+int b200p_set_profiling(b200p_handle h, int on) {
+  if (h == NULL) return B200P_E_INVALID;
+  ProfCollect(h);
+  h->profiling = on != 0;
+  for (int k = 0; k < 3; ++k) { h->kernel_ms[k] = 0.0; h->kernel_launches[k] = 0; }
+  return B200P_OK;
+}
+
+int b200p_kernel_time(b200p_handle h, int kernel, double *total_ms, uint64_t *launches) {
+  if (h == NULL || kernel < 0 || kernel > 2) return B200P_E_INVALID;
+  cudaSetDevice(h->cfg.device);
+  ProfCollect(h); /* waits for the recorded events */
+  if (total_ms != NULL) *total_ms = h->kernel_ms[kernel];
+  if (launches != NULL) *launches = h->kernel_launches[kernel];
+  return B200P_OK;
+}
 
 /* ---- device-resident path ---- */
 int b200p_parse_device_async(b200p_handle h, const void *d_text, uint64_t nbytes) {
@@ -507,17 +567,32 @@ int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes) {
     if (id < 0) return Fail(h, B200P_E_AGAIN, "all pipeline slots are in flight: call b200p_next");
   }
   if (in_place && nbytes > h->slots[id].text_cap) return Fail(h, B200P_E_INVALID, "chunk exceeds the staging buffer");
+  const void *src = text;
   if (!in_place) {
     const int rc = PrepareSlot(h, id, nbytes);
     if (rc != B200P_OK) return rc;
-    if (nbytes != 0) std::memcpy(h->slots[id].h_text, text, nbytes);
+    /* memory the caller already pinned (cudaHostAlloc / cudaHostRegister) is copied to the
+       device straight from where it lies; pageable memory goes through the staging buffer */
+    bool caller_pinned = false;
+    if (nbytes != 0) {
+      cudaPointerAttributes attr;
+      if (cudaPointerGetAttributes(&attr, text) == cudaSuccess) {
+        caller_pinned = attr.type == cudaMemoryTypeHost;
+      } else {
+        cudaGetLastError();
+      }
+    }
+    if (!caller_pinned && nbytes != 0) {
+      std::memcpy(h->slots[id].h_text, text, nbytes);
+      src = h->slots[id].h_text;
+    }
   }
   h->lent_slot = -1;
   Slot *s = &h->slots[id];
   s->nbytes = nbytes;
   s->text = s->d_text;
   if (nbytes != 0) {
-    CUDA_TRY(h, cudaMemcpyAsync(s->d_text, s->h_text, nbytes, cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(h, cudaMemcpyAsync(s->d_text, src, nbytes, cudaMemcpyHostToDevice, s->stream));
   }
   const int rc = EnqueueParse(h, s);
   if (rc != B200P_OK) return rc;

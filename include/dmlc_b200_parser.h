@@ -113,7 +113,10 @@ int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out);
  *   b200p_input_buffer  pinned staging buffer of the next free slot, to be filled in place
  *                       (e.g. by pread); capacity >= config.chunk_bytes.
  *   b200p_submit        enqueue a chunk. `text` may be the pointer b200p_input_buffer returned
- *                       (zero-copy) or any host memory (copied into the staging buffer first).
+ *                       or memory the caller pinned itself (both copied to the device from
+ *                       where they lie; caller-pinned memory must stay untouched until the
+ *                       matching b200p_next), or pageable memory (staged through the pinned
+ *                       buffer first).
  *   b200p_next          wait for the oldest submitted chunk; pointers are pinned host memory,
  *                       valid until the next b200p_next / b200p_destroy on this handle.
  * Replaces: ParserImpl::ParseNext -> FillData (src/data/parser.h:30-44, text_parser.h:93-134).
@@ -131,6 +134,19 @@ int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t
 
 /* number of kernels this handle has launched so far (bench.py's gpu_launches claim) */
 uint64_t b200p_launch_count(b200p_handle h);
+
+/*
+ * Per-kernel device time, measured with CUDA events recorded on the stream each kernel is
+ * launched on. Off by default (two extra event records per launch). b200p_kernel_time waits for
+ * the recorded launches and returns their summed duration and count since profiling was
+ * switched on. No reference counterpart (the reference only prints wall-clock MB/s,
+ * test/libsvm_parser_test.cc:27-31).
+ */
+#define B200P_KERNEL_COUNT 0 /* pass 1: WalkText<EMIT=false> */
+#define B200P_KERNEL_SCAN 1  /* ScanRanges */
+#define B200P_KERNEL_EMIT 2  /* pass 2: WalkText<EMIT=true> */
+int b200p_set_profiling(b200p_handle h, int on);
+int b200p_kernel_time(b200p_handle h, int kernel, double *total_ms, uint64_t *launches);
 
 /* library / build identification: "dmlc_b200 <version> sm_100a" */
 const char *b200p_version(void);
