@@ -14,7 +14,8 @@ LIB_PATH = os.path.join(_HERE, "lib", "libdmlc_b200.so")
 
 LIBSVM, LIBFM, CSV = 0, 1, 2
 FORMATS = {"libsvm": LIBSVM, "libfm": LIBFM, "csv": CSV}
-OK, E_INVALID, E_CUDA, E_PARSE, E_AGAIN, E_EMPTY = 0, 1, 2, 3, 4, 5
+OK, E_INVALID, E_CUDA, E_PARSE, E_AGAIN, E_EMPTY, E_CAPACITY = 0, 1, 2, 3, 4, 5, 6
+NOALLOC_MAX_BYTES = 256 << 20
 MAX_CHUNK_BYTES = 1 << 30
 
 # every symbol include/dmlc_b200_parser.h declares
@@ -22,7 +23,7 @@ EXPORTS = (
     "b200p_create", "b200p_destroy", "b200p_last_error", "b200p_parse_device",
     "b200p_parse_device_async", "b200p_parse_device_finish", "b200p_input_buffer",
     "b200p_submit", "b200p_next", "b200p_pending", "b200p_fetch", "b200p_launch_count",
-    "b200p_set_profiling", "b200p_kernel_time", "b200p_version",
+    "b200p_set_profiling", "b200p_kernel_time", "b200p_version", "b200p_parse_device_noalloc",
 )
 
 
@@ -43,6 +44,15 @@ class RowBlock(C.Structure):
                 ("qid", C.c_void_p), ("field", C.c_void_p), ("index", C.c_void_p),
                 ("value", C.c_void_p), ("text_bytes", C.c_uint64), ("index_bytes", C.c_int32),
                 ("on_device", C.c_int32)]
+
+
+class NoAllocRequest(C.Structure):
+    _fields_ = [("format", C.c_int32), ("index_bytes", C.c_int32), ("label_column", C.c_int32),
+                ("device", C.c_int32), ("stream", C.c_void_p), ("d_text", C.c_void_p),
+                ("nbytes", C.c_uint64), ("d_offset", C.c_void_p), ("d_label", C.c_void_p),
+                ("d_weight", C.c_void_p), ("d_qid", C.c_void_p), ("d_field", C.c_void_p),
+                ("d_index", C.c_void_p), ("d_value", C.c_void_p), ("cap_rows", C.c_uint64),
+                ("cap_nnz", C.c_uint64)]
 
 
 _lib = None
@@ -86,6 +96,9 @@ def load():
     lib.b200p_set_profiling.restype = C.c_int
     lib.b200p_kernel_time.argtypes = [H, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     lib.b200p_kernel_time.restype = C.c_int
+    lib.b200p_parse_device_noalloc.argtypes = [C.POINTER(NoAllocRequest), C.POINTER(RowBlock),
+                                               C.c_char_p, C.c_uint64]
+    lib.b200p_parse_device_noalloc.restype = C.c_int
     lib.b200p_version.argtypes = []
     lib.b200p_version.restype = C.c_char_p
     _lib = lib
@@ -237,3 +250,13 @@ class Parser(object):
         """submit + next for one chunk; raises ParseError where the reference would throw."""
         self.submit(data)
         return self.next()
+
+
+def parse_device_noalloc(request):
+    """b200p_parse_device_noalloc: parse with caller-owned device arrays and the library's fixed
+    scratch. Returns (rc, RowBlock, message); see include/dmlc_b200_parser.h for the limits."""
+    lib = load()
+    blk = RowBlock()
+    err = C.create_string_buffer(512)
+    rc = lib.b200p_parse_device_noalloc(C.byref(request), C.byref(blk), err, 512)
+    return rc, blk, err.value.decode()

@@ -6,6 +6,7 @@
  * usable GPU b200p_create fails with B200P_E_CUDA.
  */
 #include <cuda_runtime.h>
+#include <pthread.h>
 
 #include <algorithm>
 #include <cstdio>
@@ -636,6 +637,205 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
   }
   FillBlock(h, *s, s->host, false, out);
   h->returned_slot = id;
+  return B200P_OK;
+}
+
+
+/* ------------------------------------------------------------------------------------------
+ * b200p_parse_device_noalloc: the same count -> scan -> emit parse as b200p_parse_device, for
+ * hosts that must not allocate GPU memory while they run.
+ *
+ * Who needs this: a parser embedded in a process whose HBM is already owned by somebody else's
+ * arena -- an XGBoost/RMM pool or a deep-learning framework's caching allocator that reserved
+ * the whole card at start-up -- or one that runs next to live NCCL collectives, where a
+ * cudaMalloc / cudaFree can stall every stream of the device or simply fail because nothing is
+ * left outside the pool.  Such a caller carves its text buffer and its CSR arrays out of its own
+ * pool and hands them in; the only other memory the kernels need is their scratch (per-range
+ * counters and the chunk summary), and that lives in the fixed array below, which the CUDA
+ * module reserves once per GPU when the library is loaded and keeps until the process exits.
+ *
+ * Limit: kNoAllocMaxRanges ranges of kNoAllocRangeBytes, i.e. chunks up to 256 MiB; the array is
+ * about 640 KiB per GPU.  Larger chunks are refused, not truncated.
+ *
+ * Shared state: every call on a GPU uses the same array and finds the previous call's counters
+ * in it.  Pass 1 rewrites every counter it will read and the summary is cleared at the start of
+ * each call, so calls issued one after another are independent -- but two calls whose kernels
+ * overlap on one GPU (different streams, different threads) race on the array and corrupt each
+ * other.  Serialise them.
+ *
+ * First call on a device: resolves the device address of the array with cudaGetSymbolAddress
+ * (the host-side name `g_noalloc_scratch` is only a stand-in; handing it to a kernel would make
+ * the kernel touch unrelated memory or fault).  Make that first call outside any stream capture.
+ * ------------------------------------------------------------------------------------------ */
+namespace {
+constexpr uint32_t kNoAllocMaxRanges = 32768u;
+constexpr uint32_t kNoAllocRangeBytes = 8192u;
+constexpr uint64_t kNoAllocMaxBytes = static_cast<uint64_t>(kNoAllocMaxRanges) * kNoAllocRangeBytes;
+constexpr int kNoAllocMaxDevices = 64;
+
+struct NoAllocScratch {
+  uint32_t counts[kNumCounters * kNoAllocMaxRanges];
+  ChunkSummary summary;
+};
+
+/* file-scope scratch: one instance per GPU that loads this module, resident until exit */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+static NoAllocScratch *g_noalloc_address[kNoAllocMaxDevices]; /* device addresses, per ordinal */
+static pthread_mutex_t g_noalloc_mutex = PTHREAD_MUTEX_INITIALIZER;
+
+static void NoAllocSay(char *errbuf, uint64_t errlen, const char *msg) {
+  if (errbuf != NULL && errlen != 0) std::snprintf(errbuf, errlen, "%s", msg);
+}
+
+/* device address of the scratch on `device` (which must be current); set up once per device */
+static cudaError_t NoAllocScratchFor(int device, NoAllocScratch **out) {
+  cudaError_t e = cudaSuccess;
+  pthread_mutex_lock(&g_noalloc_mutex);
+  if (g_noalloc_address[device] == NULL) {
+    void *ptr = NULL;
+    e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e == cudaSuccess) g_noalloc_address[device] = static_cast<NoAllocScratch *>(ptr);
+  }
+  *out = g_noalloc_address[device];
+  pthread_mutex_unlock(&g_noalloc_mutex);
+  return e;
+}
+
+static void LaunchWalkPlain(int format, bool wide, const WalkParams &p, cudaStream_t s, bool emit) {
+  if (format == B200P_FORMAT_LIBSVM) {
+    if (wide) LaunchWalks<kLibSVM, uint64_t>(p, s, emit); else LaunchWalks<kLibSVM, uint32_t>(p, s, emit);
+  } else if (format == B200P_FORMAT_LIBFM) {
+    if (wide) LaunchWalks<kLibFM, uint64_t>(p, s, emit); else LaunchWalks<kLibFM, uint32_t>(p, s, emit);
+  } else {
+    if (wide) LaunchWalks<kCSV, uint64_t>(p, s, emit); else LaunchWalks<kCSV, uint32_t>(p, s, emit);
+  }
+}
+}  // namespace
+
+int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *out,
+                               char *errbuf, uint64_t errlen) {
+  if (errbuf != NULL && errlen != 0) errbuf[0] = '\0';
+  if (rq == NULL || out == NULL) return B200P_E_INVALID;
+  std::memset(out, 0, sizeof(*out));
+  if (rq->format < 0 || rq->format > 2 || (rq->index_bytes != 4 && rq->index_bytes != 8) ||
+      rq->device < 0 || rq->device >= kNoAllocMaxDevices) {
+    NoAllocSay(errbuf, errlen, "b200p_parse_device_noalloc: bad format / index_bytes / device");
+    return B200P_E_INVALID;
+  }
+  if (rq->nbytes > kNoAllocMaxBytes) {
+    if (errbuf != NULL && errlen != 0) {
+      std::snprintf(errbuf, errlen,
+                    "b200p_parse_device_noalloc: chunk of %llu bytes exceeds the fixed scratch, which "
+                    "covers at most %llu bytes per call; split the chunk after a line end or use "
+                    "b200p_parse_device",
+                    static_cast<unsigned long long>(rq->nbytes),
+                    static_cast<unsigned long long>(kNoAllocMaxBytes));
+    }
+    return B200P_E_INVALID;
+  }
+  if ((reinterpret_cast<uintptr_t>(rq->d_text) & 15u) != 0) {
+    NoAllocSay(errbuf, errlen, "b200p_parse_device_noalloc: d_text must be 16-byte aligned");
+    return B200P_E_INVALID;
+  }
+  const bool need_weight = rq->format != B200P_FORMAT_CSV;
+  const bool need_qid = rq->format == B200P_FORMAT_LIBSVM;
+  const bool need_field = rq->format == B200P_FORMAT_LIBFM;
+  if (rq->nbytes != 0 &&
+      (rq->d_text == NULL || rq->d_offset == NULL || rq->d_label == NULL || rq->d_index == NULL ||
+       rq->d_value == NULL || (need_weight && rq->d_weight == NULL) ||
+       (need_qid && rq->d_qid == NULL) || (need_field && rq->d_field == NULL))) {
+    NoAllocSay(errbuf, errlen, "b200p_parse_device_noalloc: an output array this format writes is NULL");
+    return B200P_E_INVALID;
+  }
+  out->index_bytes = rq->index_bytes;
+  out->on_device = 1;
+  out->text_bytes = rq->nbytes;
+  if (rq->nbytes == 0) return B200P_OK;
+
+#define NOALLOC_TRY(expr)                                                                     \
+  do {                                                                                        \
+    cudaError_t e_ = (expr);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      if (errbuf != NULL && errlen != 0)                                                      \
+        std::snprintf(errbuf, errlen, "b200p_parse_device_noalloc: CUDA error %s at line %d: %s", \
+                      cudaGetErrorName(e_), __LINE__, cudaGetErrorString(e_));                \
+      return B200P_E_CUDA;                                                                    \
+    }                                                                                         \
+  } while (0)
+
+  NOALLOC_TRY(cudaSetDevice(rq->device));
+  NoAllocScratch *scratch = NULL;
+  NOALLOC_TRY(NoAllocScratchFor(rq->device, &scratch));
+  cudaStream_t stream = static_cast<cudaStream_t>(rq->stream);
+
+  WalkParams p;
+  std::memset(&p, 0, sizeof(p));
+  p.text = static_cast<const uint8_t *>(rq->d_text);
+  p.size = static_cast<uint32_t>(rq->nbytes);
+  p.range_bytes = kNoAllocRangeBytes;
+  p.num_ranges = static_cast<uint32_t>((rq->nbytes + kNoAllocRangeBytes - 1) / kNoAllocRangeBytes);
+  p.label_column = rq->label_column;
+  p.counts = scratch->counts;
+  p.summary = &scratch->summary;
+  p.offset = reinterpret_cast<unsigned long long *>(rq->d_offset);
+  p.label = rq->d_label;
+  p.weight = rq->d_weight;
+  p.qid = reinterpret_cast<unsigned long long *>(rq->d_qid);
+  p.field = rq->d_field;
+  p.index = rq->d_index;
+  p.value = rq->d_value;
+  p.cap_rows = rq->cap_rows;
+  p.cap_nnz = rq->cap_nnz;
+  const bool wide = rq->index_bytes == 8;
+
+  /* the summary (totals + error word) must start from zero; the counters need no clearing
+     because pass 1 stores all five counters of every range it is launched for */
+  NOALLOC_TRY(cudaMemsetAsync(&scratch->summary, 0, sizeof(ChunkSummary), stream));
+  LaunchWalkPlain(rq->format, wide, p, stream, false);
+  ScanRanges<<<1, 1024, 0, stream>>>(scratch->counts, p.num_ranges, &scratch->summary);
+  if (rq->format == B200P_FORMAT_CSV) {
+    ZeroLabels<<<296, 256, 0, stream>>>(p.label, &scratch->summary, p.cap_rows);
+  }
+  LaunchWalkPlain(rq->format, wide, p, stream, true);
+  NOALLOC_TRY(cudaGetLastError());
+  ChunkSummary sum; /* on the caller's stack: nothing is allocated for the read-back either */
+  NOALLOC_TRY(cudaMemcpyAsync(&sum, &scratch->summary, sizeof(sum), cudaMemcpyDeviceToHost, stream));
+  NOALLOC_TRY(cudaStreamSynchronize(stream));
+#undef NOALLOC_TRY
+
+  out->rows = sum.total[kRows];
+  out->nnz = sum.total[kNnz];
+  out->n_weight = sum.total[kWeights];
+  out->n_qid = sum.total[kQids];
+  out->n_value = sum.total[kValues];
+  out->n_field = need_field ? out->nnz : 0;
+  if (sum.total[kRows] > rq->cap_rows || sum.total[kNnz] > rq->cap_nnz) {
+    /* pass 2 wrote nothing; rows / nnz tell the caller how much room this chunk needs */
+    if (errbuf != NULL && errlen != 0) {
+      std::snprintf(errbuf, errlen,
+                    "b200p_parse_device_noalloc: output arrays too small, chunk has %llu rows and "
+                    "%llu entries", sum.total[kRows], sum.total[kNnz]);
+    }
+    return B200P_E_CAPACITY;
+  }
+  if (sum.error & kErrNegativeIndex) {
+    NoAllocSay(errbuf, errlen, "Check failed: sign == true (negative value in an unsigned index/field)");
+    return B200P_E_PARSE;
+  }
+  if (sum.error & kErrValueCount) {
+    NoAllocSay(errbuf, errlen, "Check failed: offset.back() == value.size() || value.size() == 0");
+    return B200P_E_PARSE;
+  }
+  if (out->rows != 0) {
+    out->offset = rq->d_offset;
+    out->label = rq->d_label;
+    out->weight = out->n_weight ? rq->d_weight : NULL;
+    out->qid = out->n_qid ? rq->d_qid : NULL;
+    out->field = out->n_field ? rq->d_field : NULL;
+    out->index = out->nnz ? rq->d_index : NULL;
+    out->value = out->n_value ? rq->d_value : NULL;
+  }
   return B200P_OK;
 }
 

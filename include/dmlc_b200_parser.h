@@ -31,6 +31,7 @@ extern "C" {
 #define B200P_E_PARSE 3     /* input makes the reference parser throw dmlc::Error */
 #define B200P_E_AGAIN 4     /* no free pipeline slot: call b200p_next first */
 #define B200P_E_EMPTY 5     /* nothing submitted */
+#define B200P_E_CAPACITY 6  /* caller-provided output arrays are too small (no-alloc entry only) */
 
 #define B200P_FORMAT_LIBSVM 0 /* src/data/libsvm_parser.h */
 #define B200P_FORMAT_LIBFM 1  /* src/data/libfm_parser.h */
@@ -134,6 +135,50 @@ int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t
 
 /* number of kernels this handle has launched so far (bench.py's gpu_launches claim) */
 uint64_t b200p_launch_count(b200p_handle h);
+
+/*
+ * Allocation-free variant of b200p_parse_device. It has no counterpart in the reference.
+ *
+ * For callers that cannot allocate GPU memory while they run: the card was handed over in full
+ * to a memory pool at start-up (RMM under XGBoost, a framework's caching allocator), or the
+ * process is in the middle of NCCL traffic where cudaMalloc/cudaFree stalls the device. Such a
+ * caller passes the text AND every CSR array (device pointers from its own pool, capacities in
+ * elements); the kernels' scratch sits in a fixed __device__ array inside the library, about
+ * 640 KiB that each GPU loading the library keeps until exit. No handle is needed and the call
+ * performs no cudaMalloc / cudaFree / pinned allocation.
+ *
+ * Limit: nbytes <= B200P_NOALLOC_MAX_BYTES (256 MiB); larger chunks return B200P_E_INVALID with
+ * a message in errbuf. Arrays too small: B200P_E_CAPACITY, out->rows / out->nnz = what the chunk
+ * needs, nothing written. Required arrays: offset (cap_rows + 1 entries), label, index, value;
+ * weight unless CSV; qid for LibSVM; field for LibFM.
+ *
+ * The scratch is shared by all calls on a GPU and keeps the previous call's contents; the call
+ * clears what it needs cleared, so back-to-back calls are fine, but calls that overlap on the
+ * same GPU (two streams, two threads) race -- serialise them. The call synchronises `stream`
+ * before returning. The first call on each device looks up the scratch's device address
+ * (cudaGetSymbolAddress); make that first call before starting any stream capture.
+ */
+#define B200P_NOALLOC_MAX_BYTES ((uint64_t)256 << 20)
+typedef struct b200p_noalloc_request {
+  int32_t format;        /* B200P_FORMAT_* */
+  int32_t index_bytes;   /* 4 or 8 */
+  int32_t label_column;  /* CSV */
+  int32_t device;        /* CUDA device ordinal the pointers below belong to */
+  void *stream;          /* cudaStream_t to run on (NULL = default stream) */
+  const void *d_text;    /* chunk in device memory, 16-byte aligned, cut after a line end */
+  uint64_t nbytes;
+  uint64_t *d_offset;    /* outputs, all device memory owned by the caller */
+  float *d_label;
+  float *d_weight;
+  uint64_t *d_qid;
+  void *d_field;
+  void *d_index;
+  float *d_value;
+  uint64_t cap_rows;     /* rows the row-sized arrays hold (d_offset holds cap_rows + 1) */
+  uint64_t cap_nnz;      /* entries d_field / d_index / d_value hold */
+} b200p_noalloc_request;
+int b200p_parse_device_noalloc(const b200p_noalloc_request *request, b200p_rowblock *out,
+                               char *errbuf, uint64_t errlen);
 
 /*
  * Per-kernel device time, measured with CUDA events recorded on the stream each kernel is
