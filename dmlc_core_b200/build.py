@@ -112,6 +112,11 @@ def build_oracle(force=False):
     if os.path.isdir("/root/reference/src") and (force or _stale(
             ref, [os.path.join(odir, "ref_shim.cc"), os.path.join(odir, "Makefile")])):
         _run(["make", "-s", "-C", odir, "ref"])
+    dropin = os.path.join(odir, "_ref", "libdmlc_dropin.so")
+    if os.path.isdir("/root/reference/src") and os.path.exists(os.path.join(LIB, "libdmlc_b200.so")) \
+            and (force or _stale(dropin, _glob(os.path.join(PKG, "src"), (".cc", ".h")) +
+                                 [os.path.join(odir, "Makefile")])):
+        _run(["make", "-s", "-C", odir, "dropin"])
     return os.path.join(odir, "_build", "liboracle.so")
 
 

@@ -235,6 +235,8 @@ static WalkParams MakeParams(const b200p_handle h, const Slot &s) {
   p.num_ranges = static_cast<uint32_t>((s.nbytes + h->range_bytes - 1) / h->range_bytes);
   p.label_column = h->cfg.label_column;
   p.counts = s.d_counts;
+  p.num_tiles = (p.num_ranges + kScanTile - 1) / kScanTile;
+  p.tile_base = s.d_counts + static_cast<size_t>(kNumCounters) * p.num_ranges;
   p.summary = s.d_summary;
   p.offset = s.dev.offset;
   p.label = s.dev.label;
@@ -278,7 +280,9 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
     s->d_counts = NULL;
     s->counts_cap = 0;
     const uint64_t cap = ranges + ranges / 4 + 64;
-    CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&s->d_counts), cap * kNumCounters * sizeof(uint32_t)));
+    /* per-range counters followed by the per-tile bases of the scan */
+    CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&s->d_counts),
+                           (cap + cap / kScanTile + 2) * kNumCounters * sizeof(uint32_t)));
     s->counts_cap = cap;
   }
   uint64_t want_rows, want_nnz;
@@ -293,9 +297,10 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
   LaunchWalk(h, p, s->stream, false);
   ProfEnd(h, s->stream);
   ProfBegin(h, B200P_KERNEL_SCAN, s->stream);
-  ScanRanges<<<1, 1024, 0, s->stream>>>(s->d_counts, p.num_ranges, s->d_summary);
+  ScanTiles<<<p.num_tiles, kScanTile, 0, s->stream>>>(p.counts, p.num_ranges, p.tile_base, p.num_tiles);
+  ScanFinish<<<1, kScanTile, 0, s->stream>>>(p.tile_base, p.num_tiles, p.num_ranges, s->d_summary);
   ProfEnd(h, s->stream);
-  h->launches += 2;
+  h->launches += 3;
   CUDA_TRY(h, cudaGetLastError());
   return EnqueueEmit(h, s);
 }
@@ -675,6 +680,7 @@ constexpr int kNoAllocMaxDevices = 64;
 
 struct NoAllocScratch {
   uint32_t counts[kNumCounters * kNoAllocMaxRanges];
+  uint32_t tile_base[kNumCounters * (kNoAllocMaxRanges / kScanTile)];
   ChunkSummary summary;
 };
 
@@ -777,6 +783,8 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
   p.num_ranges = static_cast<uint32_t>((rq->nbytes + kNoAllocRangeBytes - 1) / kNoAllocRangeBytes);
   p.label_column = rq->label_column;
   p.counts = scratch->counts;
+  p.num_tiles = (p.num_ranges + kScanTile - 1) / kScanTile;
+  p.tile_base = scratch->tile_base;
   p.summary = &scratch->summary;
   p.offset = reinterpret_cast<unsigned long long *>(rq->d_offset);
   p.label = rq->d_label;
@@ -793,7 +801,8 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
      because pass 1 stores all five counters of every range it is launched for */
   NOALLOC_TRY(cudaMemsetAsync(&scratch->summary, 0, sizeof(ChunkSummary), stream));
   LaunchWalkPlain(rq->format, wide, p, stream, false);
-  ScanRanges<<<1, 1024, 0, stream>>>(scratch->counts, p.num_ranges, &scratch->summary);
+  ScanTiles<<<p.num_tiles, kScanTile, 0, stream>>>(p.counts, p.num_ranges, p.tile_base, p.num_tiles);
+  ScanFinish<<<1, kScanTile, 0, stream>>>(p.tile_base, p.num_tiles, p.num_ranges, &scratch->summary);
   if (rq->format == B200P_FORMAT_CSV) {
     ZeroLabels<<<296, 256, 0, stream>>>(p.label, &scratch->summary, p.cap_rows);
   }

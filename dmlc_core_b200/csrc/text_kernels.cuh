@@ -10,7 +10,7 @@
  * Shape of the computation (HBM-bound byte work, no tensor cores):
  *
  *   pass 1  WalkText<..., EMIT=false>   count rows / nnz / values / weights / qids per byte range
- *   scan    ScanRanges                  exclusive prefix over ranges -> where each range writes
+ *   scan    ScanTiles + ScanFinish      exclusive prefix over ranges -> where each range writes
  *   pass 2  WalkText<..., EMIT=true>    same walk, now converting tokens and storing CSR arrays
  *
  * The chunk is cut into fixed byte ranges; a warp owns the lines that START inside its range
@@ -53,9 +53,10 @@ constexpr int kWarpsPerCta = 8;
 constexpr int kCtaThreads = kWarpsPerCta * 32;
 constexpr int kTokenQueue = 320;       /* < 32 left over + <= 256 new digit runs per step */
 constexpr int kFieldQueue = 576;       /* CSV: < 32 left over + <= 512 field starts per step */
+constexpr int kScanTile = 1024;         /* ranges scanned by one CTA of the prefix-sum kernels */
 constexpr int kRoleQueue = 64;         /* < 32 left over + <= 32 new per token group */
 
-/* Result header written by ScanRanges (device memory, copied to the host per chunk). */
+/* Result header written by ScanFinish (device memory, copied to the host per chunk). */
 struct ChunkSummary {
   unsigned long long total[kNumCounters];
   unsigned int error;
@@ -68,8 +69,10 @@ struct WalkParams {
   uint32_t range_bytes;    /* multiple of kStepBytes */
   uint32_t num_ranges;
   int32_t label_column;    /* CSV */
-  uint32_t *counts;        /* [kNumCounters][num_ranges]: pass 1 writes counts, scan rewrites
-                              them in place as exclusive prefixes, pass 2 reads them */
+  uint32_t *counts;        /* [kNumCounters][num_ranges]: pass 1 writes counts, the scan rewrites
+                              them in place as exclusive prefixes within tiles of kScanTile */
+  uint32_t *tile_base;     /* [kNumCounters][num_tiles]: exclusive prefix of the tile totals */
+  uint32_t num_tiles;
   ChunkSummary *summary;
   /* outputs (pass 2) and their capacities in elements */
   unsigned long long *offset;
@@ -550,7 +553,10 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   st.error = 0;
   if (EMIT) {
 #pragma unroll
-    for (int c = 0; c < kNumCounters; ++c) st.seen[c] = prm.counts[c * prm.num_ranges + range];
+    for (int c = 0; c < kNumCounters; ++c) {
+      st.seen[c] = prm.counts[c * prm.num_ranges + range] +
+                   prm.tile_base[c * prm.num_tiles + range / kScanTile];
+    }
     st.w_label = st.seen[kRows];
     st.w_index = st.seen[kNnz];
     st.w_value = st.seen[kValues];
@@ -665,52 +671,68 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
 }
 
 /*
- * Exclusive prefix sums of the per-range counters, in place, plus the chunk totals and the
- * RowBlock consistency check of the reference (row_block.h:177).  One CTA: the counter arrays
- * are tiny (5 x chunk_bytes / range_bytes words).
+ * Exclusive prefix sums of the per-range counters, in two small launches.
+ *
+ * ScanTiles: CTA t scans ranges [t*1024, (t+1)*1024) of all five counters in place (coalesced:
+ * thread i <-> range t*1024+i) and stores the tile's totals.  ScanFinish: one CTA turns the tile
+ * totals into exclusive tile bases (in place), the chunk totals and the RowBlock consistency
+ * check of the reference (row_block.h:177).  Pass 2 adds counts[range] + tile_base[range/1024].
  */
-__global__ void __launch_bounds__(1024) ScanRanges(uint32_t *counts, uint32_t num_ranges,
-                                                   ChunkSummary *summary) {
-  __shared__ uint32_t partial[kNumCounters][1024];
-  const uint32_t tid = threadIdx.x;
-  const uint32_t per = (num_ranges + 1023u) / 1024u;
-  const uint32_t lo = min(tid * per, num_ranges);
-  const uint32_t hi = min(lo + per, num_ranges);
-  uint32_t sum[kNumCounters];
-#pragma unroll
-  for (int c = 0; c < kNumCounters; ++c) {
-    uint32_t s = 0;
-    for (uint32_t i = lo; i < hi; ++i) s += counts[c * num_ranges + i];
-    sum[c] = s;
-    partial[c][tid] = s;
+__device__ __forceinline__ uint32_t BlockExclusiveScan(uint32_t v, uint32_t *warp_sums /*[32]*/,
+                                                       uint32_t *total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = WarpInclusiveSum(v, lane);
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t w = warp_sums[lane];
+    const uint32_t wi = WarpInclusiveSum(w, lane);
+    warp_sums[lane] = wi - w; /* exclusive base of each warp */
+    if (lane == 31) *total = wi;
   }
   __syncthreads();
-  /* Hillis-Steele inclusive scan across the 1024 partials of each counter */
-  for (uint32_t d = 1; d < 1024u; d <<= 1) {
-    uint32_t add[kNumCounters];
-#pragma unroll
-    for (int c = 0; c < kNumCounters; ++c) add[c] = tid >= d ? partial[c][tid - d] : 0u;
-    __syncthreads();
-#pragma unroll
-    for (int c = 0; c < kNumCounters; ++c) partial[c][tid] += add[c];
-    __syncthreads();
-  }
+  const uint32_t r = incl - v + warp_sums[warp];
+  return r;
+}
+
+__global__ void __launch_bounds__(kScanTile) ScanTiles(uint32_t *counts, uint32_t num_ranges,
+                                                       uint32_t *tile_base, uint32_t num_tiles) {
+  __shared__ uint32_t warp_sums[kNumCounters][32];
+  __shared__ uint32_t totals[kNumCounters];
+  const uint32_t i = blockIdx.x * kScanTile + threadIdx.x;
 #pragma unroll
   for (int c = 0; c < kNumCounters; ++c) {
-    uint32_t run = partial[c][tid] - sum[c];
-    for (uint32_t i = lo; i < hi; ++i) {
-      const uint32_t v = counts[c * num_ranges + i];
-      counts[c * num_ranges + i] = run;
-      run += v;
-    }
+    const uint32_t v = i < num_ranges ? counts[c * num_ranges + i] : 0u;
+    const uint32_t ex = BlockExclusiveScan(v, warp_sums[c], &totals[c]);
+    if (i < num_ranges) counts[c * num_ranges + i] = ex;
   }
-  if (tid == 1023u) {
+  __syncthreads();
+  if (threadIdx.x < kNumCounters) tile_base[threadIdx.x * num_tiles + blockIdx.x] = totals[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(kScanTile) ScanFinish(uint32_t *tile_base, uint32_t num_tiles,
+                                                        uint32_t num_ranges, ChunkSummary *summary) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t total;
+  __shared__ unsigned long long grand[kNumCounters];
+  for (int c = 0; c < kNumCounters; ++c) {
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < num_tiles; base += kScanTile) {
+      const uint32_t i = base + threadIdx.x;
+      const uint32_t v = i < num_tiles ? tile_base[c * num_tiles + i] : 0u;
+      const uint32_t ex = BlockExclusiveScan(v, warp_sums, &total);
+      if (i < num_tiles) tile_base[c * num_tiles + i] = carry + ex;
+      carry += total;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) grand[c] = carry;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
     unsigned int err = 0;
 #pragma unroll
-    for (int c = 0; c < kNumCounters; ++c) summary->total[c] = partial[c][1023];
-    if (partial[kValues][1023] != 0u && partial[kValues][1023] != partial[kNnz][1023]) {
-      err |= kErrValueCount;
-    }
+    for (int c = 0; c < kNumCounters; ++c) summary->total[c] = grand[c];
+    if (grand[kValues] != 0ull && grand[kValues] != grand[kNnz]) err |= kErrValueCount;
     summary->error = err;
     summary->ranges = num_ranges;
   }

@@ -1,0 +1,370 @@
+/*
+ * dmlc::Parser<IndexType> on the B200: the drop-in for what the reference builds in
+ * src/data.cc:21-85 (factories, CreateParser_, Parser<I>::Create) on top of
+ * TextParserBase / LibSVMParser / LibFMParser / CSVParser / ThreadedParser.
+ *
+ * Host side only: reads whole-line chunks of its InputSplit partition straight into the pinned
+ * staging buffers of the C ABI (include/dmlc_b200_parser.h), keeps `depth` chunks in flight on
+ * the GPU, and exposes each parsed chunk as one RowBlock whose arrays live in pinned host
+ * memory.  All parsing happens in the sm_100a kernels; there is no CPU fallback.
+ */
+#include <dmlc/data.h>
+#include <dmlc/io.h>
+#include <dmlc/logging.h>
+#include <dmlc/parameter.h>
+#include <dmlc/timer.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+#include "../../include/dmlc_b200_parser.h"
+#include "./uri_spec.h"
+/*
+ * DMLC_B200 is defined by this package's own <dmlc/base.h>.  Built against the reference's
+ * headers instead (the true drop-in build) the parser takes whatever
+ * InputSplit the reference's InputSplit::Create returns and copies each chunk into pinned memory;
+ * built here it recognises its own TextSplit and lets it read straight into the pinned buffers.
+ */
+#if defined(DMLC_B200)
+#include "./text_split.h"
+#define B200_HAVE_TEXT_SPLIT 1
+#else
+#define B200_HAVE_TEXT_SPLIT 0
+#endif
+
+namespace dmlc {
+namespace b200 {
+
+static int EnvInt(const char *name, int fallback) {
+  const char *v = std::getenv(name);
+  return (v != NULL && *v != '\0') ? std::atoi(v) : fallback;
+}
+
+/*
+ * One parser instance = one partition of the input on one GPU.
+ * Environment knobs (GPU-side settings cannot ride in the URI: CSVParserParam::Init rejects
+ * unknown keys, reference csv_parser.h:50 + parameter.h:405-418):
+ *   DMLC_B200_DEVICE    CUDA device ordinal (default 0)
+ *   DMLC_B200_CHUNK_MB  chunk size in MiB (default 64; the reference uses 8, input_split_base.h:40)
+ *   DMLC_B200_DEPTH     chunks in flight (default 3)
+ */
+template <typename IndexType>
+class B200TextParser : public Parser<IndexType> {
+ public:
+  B200TextParser(InputSplit *source, int format, int label_column)
+      : source_(source), text_(NULL), handle_(NULL),
+        bytes_read_(0), exhausted_(false) {
+    std::memset(&block_, 0, sizeof(block_));
+#if B200_HAVE_TEXT_SPLIT
+    text_ = dynamic_cast<TextSplit *>(source);
+#endif
+    b200p_config cfg;
+    std::memset(&cfg, 0, sizeof(cfg));
+    cfg.format = format;
+    cfg.index_bytes = static_cast<int32_t>(sizeof(IndexType));
+    cfg.label_column = label_column;
+    cfg.device = EnvInt("DMLC_B200_DEVICE", 0);
+    chunk_bytes_ = static_cast<size_t>(std::max(1, EnvInt("DMLC_B200_CHUNK_MB", 64))) << 20;
+    chunk_bytes_ = std::min<size_t>(chunk_bytes_, B200P_MAX_CHUNK_BYTES);
+    cfg.chunk_bytes = chunk_bytes_;
+    depth_ = std::max(1, std::min(8, EnvInt("DMLC_B200_DEPTH", 3)));
+    cfg.depth = depth_;
+    const int rc = b200p_create(&cfg, &handle_);
+    if (rc != B200P_OK) {
+      const std::string why = b200p_last_error(NULL);
+      delete source_;
+      source_ = NULL;
+      LOG(FATAL) << "dmlc_core_b200: cannot create the GPU parser: " << why;
+    }
+    if (text_ == NULL) source_->HintChunkSize(chunk_bytes_);
+  }
+
+  virtual ~B200TextParser() {
+    b200p_destroy(handle_);
+    delete source_;
+  }
+
+  virtual void BeforeFirst(void) {
+    /* discard what is still in flight, then rewind the source (reference text_parser.h:40-42;
+       like there, BytesRead keeps counting across passes) */
+    b200p_rowblock dropped;
+    while (b200p_pending(handle_) > 0) {
+      if (b200p_next(handle_, &dropped) != B200P_OK) break;
+    }
+    source_->BeforeFirst();
+    exhausted_ = false;
+  }
+
+  virtual bool Next(void) {
+    for (;;) {
+      Feed();
+      if (b200p_pending(handle_) == 0) return false;
+      b200p_rowblock b;
+      Check(b200p_next(handle_, &b));
+      bytes_read_ += b.text_bytes;
+      if (b.rows == 0) continue;  /* chunks without rows are skipped (reference parser.h:33-38) */
+      block_.size = static_cast<size_t>(b.rows);
+      block_.offset = reinterpret_cast<const size_t *>(b.offset);
+      block_.label = b.label;
+      block_.weight = b.weight;
+      block_.qid = b.qid;
+      block_.field = static_cast<const IndexType *>(b.field);
+      block_.index = static_cast<const IndexType *>(b.index);
+      block_.value = b.value;
+      return true;
+    }
+  }
+
+  virtual const RowBlock<IndexType> &Value(void) const { return block_; }
+  virtual size_t BytesRead(void) const { return bytes_read_; }
+
+ private:
+  /* keep the pipeline full: read chunks and enqueue them until `depth` are in flight */
+  void Feed() {
+    while ((!exhausted_ || !backlog_.empty()) && b200p_pending(handle_) < depth_) {
+#if B200_HAVE_TEXT_SPLIT
+      if (text_ != NULL) {
+        void *pinned = NULL;
+        uint64_t cap = 0;
+        Check(b200p_input_buffer(handle_, &pinned, &cap));
+        size_t n = text_->ReadLines(pinned, static_cast<size_t>(cap));
+        if (n == TextSplit::kLineTooLong) {
+          /* a single line longer than the staging buffer: read it through a growing heap
+             buffer; b200p_submit then enlarges the slot */
+          size_t big = static_cast<size_t>(cap);
+          do {
+            big *= 2;
+            CHECK(big <= B200P_MAX_CHUNK_BYTES) << "a single line exceeds " << B200P_MAX_CHUNK_BYTES << " bytes";
+            spill_.resize(big);
+            n = text_->ReadLines(spill_.data(), big);
+          } while (n == TextSplit::kLineTooLong);
+          if (n == 0) { exhausted_ = true; break; }
+          Check(b200p_submit(handle_, spill_.data(), n));
+          continue;
+        }
+        if (n == 0) { exhausted_ = true; break; }
+        Check(b200p_submit(handle_, pinned, n));
+        continue;
+      }
+#endif
+      {
+        /* any other InputSplit: its chunks are copied into the staging buffer by b200p_submit
+           (the Blob dies at the next NextChunk); oversized chunks are cut at line ends */
+        if (!backlog_.empty()) {
+          Check(b200p_submit(handle_, backlog_.front().data(), backlog_.front().size()));
+          backlog_.erase(backlog_.begin());
+          continue;
+        }
+        InputSplit::Blob chunk;
+        if (!source_->NextChunk(&chunk)) { exhausted_ = true; break; }
+        const char *base = static_cast<const char *>(chunk.dptr);
+        if (chunk.size <= B200P_MAX_CHUNK_BYTES) {
+          Check(b200p_submit(handle_, base, chunk.size));
+          continue;
+        }
+        size_t done = 0;
+        while (done < chunk.size) {
+          size_t n = std::min<size_t>(chunk.size - done, B200P_MAX_CHUNK_BYTES);
+          if (done + n < chunk.size) {
+            while (n > 1 && base[done + n - 1] != '\n' && base[done + n - 1] != '\r') --n;
+          }
+          backlog_.push_back(std::string(base + done, n));
+          done += n;
+        }
+      }
+    }
+  }
+
+  void Check(int rc) {
+    if (rc == B200P_OK) return;
+    /* B200P_E_PARSE carries the reference's CHECK text; everything surfaces as dmlc::Error */
+    LOG(FATAL) << b200p_last_error(handle_);
+  }
+
+  InputSplit *source_;
+#if B200_HAVE_TEXT_SPLIT
+  TextSplit *text_;
+#else
+  void *text_;
+#endif
+  b200p_handle handle_;
+  RowBlock<IndexType> block_;
+  size_t bytes_read_;
+  size_t chunk_bytes_;
+  int depth_;
+  bool exhausted_;
+  std::vector<char> spill_;
+  std::vector<std::string> backlog_;
+};
+
+/* ---- factories: same signatures and argument handling as reference src/data.cc:21-60 ---- */
+template <typename IndexType>
+Parser<IndexType> *CreateLibSVMParser(const std::string &path,
+                                      const std::map<std::string, std::string> &args,
+                                      unsigned part_index, unsigned num_parts) {
+  InputSplit *source = InputSplit::Create(path.c_str(), part_index, num_parts, "text");
+  return new B200TextParser<IndexType>(source, B200P_FORMAT_LIBSVM, -1);
+}
+
+template <typename IndexType>
+Parser<IndexType> *CreateLibFMParser(const std::string &path,
+                                     const std::map<std::string, std::string> &args,
+                                     unsigned part_index, unsigned num_parts) {
+  InputSplit *source = InputSplit::Create(path.c_str(), part_index, num_parts, "text");
+  return new B200TextParser<IndexType>(source, B200P_FORMAT_LIBFM, -1);
+}
+
+template <typename IndexType>
+Parser<IndexType> *CreateCSVParser(const std::string &path,
+                                   const std::map<std::string, std::string> &args,
+                                   unsigned part_index, unsigned num_parts) {
+  /* CSVParserParam (reference csv_parser.h:22-32): format (must be "csv"), label_column
+     (default -1); any other key is a ParamError (parameter.h:136-142,405-418) */
+  int label_column = -1;
+  for (std::map<std::string, std::string>::const_iterator it = args.begin(); it != args.end(); ++it) {
+    if (it->first == "format") {
+      CHECK_EQ(it->second, "csv");
+    } else if (it->first == "label_column") {
+      char *end = NULL;
+      const long v = std::strtol(it->second.c_str(), &end, 10);
+      if (end == it->second.c_str() || *end != '\0') {
+        throw ParamError("Invalid Parameter format for label_column expect int but value='" +
+                         it->second + "'");
+      }
+      label_column = static_cast<int>(v);
+    } else {
+      throw ParamError("Cannot find argument '" + it->first +
+                       "', Possible Arguments:\n----------------\nformat : string, optional, "
+                       "default='csv'\n    File format.\nlabel_column : int, optional, default=-1\n"
+                       "    Column index that will put into label.\n");
+    }
+  }
+  InputSplit *source = InputSplit::Create(path.c_str(), part_index, num_parts, "text");
+  return new B200TextParser<IndexType>(source, B200P_FORMAT_CSV, label_column);
+}
+
+/* type lookup: reference CreateParser_, src/data.cc:62-85 */
+template <typename IndexType>
+Parser<IndexType> *CreateParserImpl(const char *uri, unsigned part_index, unsigned num_parts,
+                                    const char *type) {
+  std::string ptype = type;
+  UriSpec spec(uri, part_index, num_parts);
+  if (ptype == "auto") {
+    ptype = spec.args.count("format") != 0 ? spec.args.at("format") : std::string("libsvm");
+  }
+  const ParserFactoryReg<IndexType> *entry = Registry<ParserFactoryReg<IndexType> >::Get()->Find(ptype);
+  if (entry == NULL) LOG(FATAL) << "Unknown data type " << ptype;
+  return (*entry->body)(spec.uri, spec.args, part_index, num_parts);
+}
+
+/*
+ * RowBlockIter back-end: everything in host memory (reference BasicRowIter,
+ * src/data/basic_row_iter.h:62-82, with RowBlockContainer::Push, row_block.h:122-166).
+ */
+template <typename IndexType>
+class InMemoryRowIter : public RowBlockIter<IndexType> {
+ public:
+  explicit InMemoryRowIter(Parser<IndexType> *parser) : at_head_(true), max_index_(0) {
+    offset_.push_back(0);
+    const double t0 = GetTime();
+    try {
+      while (parser->Next()) Append(parser->Value());
+    } catch (...) {
+      delete parser;
+      throw;
+    }
+    const double dt = GetTime() - t0;
+    LOG(INFO) << "finish reading at " << (parser->BytesRead() >> 20UL) / (dt > 0 ? dt : 1e-9) << " MB/sec";
+    delete parser;
+    block_.size = label_.size();
+    block_.offset = BeginPtr(offset_);
+    block_.label = BeginPtr(label_);
+    block_.weight = BeginPtr(weight_);
+    block_.qid = BeginPtr(qid_);
+    block_.field = BeginPtr(field_);
+    block_.index = BeginPtr(index_);
+    block_.value = BeginPtr(value_);
+    /* same consistency rules as RowBlockContainer::GetBlock (row_block.h:173-177) */
+    CHECK_EQ(offset_.back(), index_.size());
+    CHECK(offset_.back() == value_.size() || value_.size() == 0);
+  }
+  virtual void BeforeFirst(void) { at_head_ = true; }
+  virtual bool Next(void) {
+    const bool had = at_head_;
+    at_head_ = false;
+    return had;
+  }
+  virtual const RowBlock<IndexType> &Value(void) const { return block_; }
+  virtual size_t NumCol(void) const { return static_cast<size_t>(max_index_) + 1; }
+
+ private:
+  void Append(const RowBlock<IndexType> &b) {
+    const size_t base = b.offset[0], nnz = b.offset[b.size] - base, shift = offset_.back();
+    label_.insert(label_.end(), b.label, b.label + b.size);
+    if (b.weight != NULL) weight_.insert(weight_.end(), b.weight, b.weight + b.size);
+    if (b.qid != NULL) qid_.insert(qid_.end(), b.qid, b.qid + b.size);
+    if (b.field != NULL) field_.insert(field_.end(), b.field + base, b.field + base + nnz);
+    index_.insert(index_.end(), b.index + base, b.index + base + nnz);
+    for (size_t i = 0; i < nnz; ++i) max_index_ = std::max(max_index_, b.index[base + i]);
+    if (b.value != NULL) value_.insert(value_.end(), b.value + base, b.value + base + nnz);
+    for (size_t i = 1; i <= b.size; ++i) offset_.push_back(shift + b.offset[i] - base);
+  }
+  bool at_head_;
+  IndexType max_index_;
+  RowBlock<IndexType> block_;
+  std::vector<size_t> offset_;
+  std::vector<real_t> label_, weight_, value_;
+  std::vector<uint64_t> qid_;
+  std::vector<IndexType> field_, index_;
+};
+
+template <typename IndexType>
+RowBlockIter<IndexType> *CreateIterImpl(const char *uri, unsigned part_index, unsigned num_parts,
+                                        const char *type) {
+  UriSpec spec(uri, part_index, num_parts);
+  CHECK(spec.cache_file.empty())
+      << "#cachefile (DiskRowIter) is not provided by dmlc_core_b200 yet";
+  /* strip the cache suffix only; the ?args travel on to the parser factory */
+  std::string no_cache = uri;
+  const size_t hash = no_cache.find('#');
+  if (hash != std::string::npos) no_cache.resize(hash);
+  return new InMemoryRowIter<IndexType>(CreateParserImpl<IndexType>(no_cache.c_str(), part_index, num_parts, type));
+}
+
+}  // namespace b200
+
+/* ---- the public entry points, specialised for the two index widths like src/data.cc:113-147 */
+template <>
+Parser<uint32_t> *Parser<uint32_t>::Create(const char *uri, unsigned part_index, unsigned num_parts,
+                                           const char *type) {
+  return b200::CreateParserImpl<uint32_t>(uri, part_index, num_parts, type);
+}
+template <>
+Parser<uint64_t> *Parser<uint64_t>::Create(const char *uri, unsigned part_index, unsigned num_parts,
+                                           const char *type) {
+  return b200::CreateParserImpl<uint64_t>(uri, part_index, num_parts, type);
+}
+template <>
+RowBlockIter<uint32_t> *RowBlockIter<uint32_t>::Create(const char *uri, unsigned part_index,
+                                                       unsigned num_parts, const char *type) {
+  return b200::CreateIterImpl<uint32_t>(uri, part_index, num_parts, type);
+}
+template <>
+RowBlockIter<uint64_t> *RowBlockIter<uint64_t>::Create(const char *uri, unsigned part_index,
+                                                       unsigned num_parts, const char *type) {
+  return b200::CreateIterImpl<uint64_t>(uri, part_index, num_parts, type);
+}
+
+/* registry singletons + the five stock registrations (src/data.cc:150-158; csv: uint32_t only) */
+DMLC_REGISTRY_ENABLE(ParserFactoryReg<uint32_t>);
+DMLC_REGISTRY_ENABLE(ParserFactoryReg<uint64_t>);
+DMLC_REGISTER_DATA_PARSER(uint32_t, libsvm, b200::CreateLibSVMParser<uint32_t>);
+DMLC_REGISTER_DATA_PARSER(uint64_t, libsvm, b200::CreateLibSVMParser<uint64_t>);
+DMLC_REGISTER_DATA_PARSER(uint32_t, libfm, b200::CreateLibFMParser<uint32_t>);
+DMLC_REGISTER_DATA_PARSER(uint64_t, libfm, b200::CreateLibFMParser<uint64_t>);
+DMLC_REGISTER_DATA_PARSER(uint32_t, csv, b200::CreateCSVParser<uint32_t>);
+
+}  // namespace dmlc

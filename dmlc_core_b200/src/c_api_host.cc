@@ -1,0 +1,183 @@
+/*
+ * extern "C" access to the C++ host layer (dmlc::Parser / RowBlockIter / InputSplit as provided
+ * by this package) for language bindings and for the Python test-suite, which drives the C++
+ * API exactly like the reference's drivers do (reference test/libsvm_parser_test.cc:14-34,
+ * test/csv_parser_test.cc:22-57, test/dataiter_test.cc).
+ */
+#include <dmlc/data.h>
+#include <dmlc/io.h>
+
+#include <cstdio>
+#include <cstring>
+
+extern "C" {
+
+typedef struct dmlcb_block {
+  uint64_t size;
+  const uint64_t *offset;
+  const float *label;
+  const float *weight;
+  const uint64_t *qid;
+  const void *field;
+  const void *index;
+  const float *value;
+} dmlcb_block;
+
+struct dmlcb_parser {
+  int index_bytes;
+  dmlc::Parser<uint32_t> *p32;
+  dmlc::Parser<uint64_t> *p64;
+};
+
+}  // extern "C"
+
+template <typename I>
+static void Export(const dmlc::RowBlock<I> &b, dmlcb_block *out) {
+  out->size = b.size;
+  out->offset = reinterpret_cast<const uint64_t *>(b.offset);
+  out->label = b.label;
+  out->weight = b.weight;
+  out->qid = b.qid;
+  out->field = b.field;
+  out->index = b.index;
+  out->value = b.value;
+}
+
+extern "C" {
+
+static void Say(char *err, uint64_t errlen, const char *what) {
+  if (err != NULL && errlen != 0) std::snprintf(err, errlen, "%s", what);
+}
+
+void *dmlcb_parser_create(const char *uri, unsigned part, unsigned nparts, const char *type,
+                          int index_bytes, char *err, uint64_t errlen) {
+  dmlcb_parser *h = new dmlcb_parser();
+  h->index_bytes = index_bytes;
+  h->p32 = NULL;
+  h->p64 = NULL;
+  try {
+    if (index_bytes == 8) {
+      h->p64 = dmlc::Parser<uint64_t>::Create(uri, part, nparts, type);
+    } else {
+      h->p32 = dmlc::Parser<uint32_t>::Create(uri, part, nparts, type);
+    }
+  } catch (const std::exception &e) {
+    Say(err, errlen, e.what());
+    delete h;
+    return NULL;
+  }
+  return h;
+}
+
+/* 1: a block was produced; 0: end of data; -1: dmlc::Error (message in err) */
+int dmlcb_parser_next(void *handle, dmlcb_block *out, char *err, uint64_t errlen) {
+  dmlcb_parser *h = static_cast<dmlcb_parser *>(handle);
+  try {
+    if (h->p64 != NULL) {
+      if (!h->p64->Next()) return 0;
+      Export(h->p64->Value(), out);
+    } else {
+      if (!h->p32->Next()) return 0;
+      Export(h->p32->Value(), out);
+    }
+  } catch (const std::exception &e) {
+    Say(err, errlen, e.what());
+    return -1;
+  }
+  return 1;
+}
+
+void dmlcb_parser_before_first(void *handle) {
+  dmlcb_parser *h = static_cast<dmlcb_parser *>(handle);
+  if (h->p64 != NULL) h->p64->BeforeFirst(); else h->p32->BeforeFirst();
+}
+
+uint64_t dmlcb_parser_bytes_read(void *handle) {
+  dmlcb_parser *h = static_cast<dmlcb_parser *>(handle);
+  return h->p64 != NULL ? h->p64->BytesRead() : h->p32->BytesRead();
+}
+
+void dmlcb_parser_free(void *handle) {
+  dmlcb_parser *h = static_cast<dmlcb_parser *>(handle);
+  if (h == NULL) return;
+  delete h->p64;
+  delete h->p32;
+  delete h;
+}
+
+/* RowBlockIter<I>::Create + NumCol (reference test/dataiter_test.cc); the single block stays
+   valid until dmlcb_rowiter_free */
+struct dmlcb_rowiter {
+  dmlc::RowBlockIter<uint32_t> *i32;
+  dmlc::RowBlockIter<uint64_t> *i64;
+};
+
+void *dmlcb_rowiter_create(const char *uri, unsigned part, unsigned nparts, const char *type,
+                           int index_bytes, dmlcb_block *out, uint64_t *num_col, char *err,
+                           uint64_t errlen) {
+  dmlcb_rowiter *h = new dmlcb_rowiter();
+  h->i32 = NULL;
+  h->i64 = NULL;
+  try {
+    if (index_bytes == 8) {
+      h->i64 = dmlc::RowBlockIter<uint64_t>::Create(uri, part, nparts, type);
+      h->i64->BeforeFirst();
+      if (h->i64->Next()) Export(h->i64->Value(), out);
+      *num_col = h->i64->NumCol();
+    } else {
+      h->i32 = dmlc::RowBlockIter<uint32_t>::Create(uri, part, nparts, type);
+      h->i32->BeforeFirst();
+      if (h->i32->Next()) Export(h->i32->Value(), out);
+      *num_col = h->i32->NumCol();
+    }
+  } catch (const std::exception &e) {
+    Say(err, errlen, e.what());
+    delete h->i32;
+    delete h->i64;
+    delete h;
+    return NULL;
+  }
+  return h;
+}
+
+void dmlcb_rowiter_free(void *handle) {
+  dmlcb_rowiter *h = static_cast<dmlcb_rowiter *>(handle);
+  if (h == NULL) return;
+  delete h->i32;
+  delete h->i64;
+  delete h;
+}
+
+/*
+ * InputSplit::Create(uri, part, nparts, "text") drained with NextChunk (mode 0) or NextRecord
+ * (mode 1, records re-joined with '\n'): the bytes of the partition, for checking the
+ * partition arithmetic without a GPU. Returns the total length, or UINT64_MAX on error.
+ */
+uint64_t dmlcb_split_bytes(const char *uri, unsigned part, unsigned nparts, int mode,
+                           uint64_t chunk_hint, char *buf, uint64_t cap, uint64_t *pieces,
+                           char *err, uint64_t errlen) {
+  uint64_t total = 0, n = 0;
+  try {
+    dmlc::InputSplit *split = dmlc::InputSplit::Create(uri, part, nparts, "text");
+    if (chunk_hint != 0) split->HintChunkSize(chunk_hint);
+    dmlc::InputSplit::Blob blob;
+    while (mode == 0 ? split->NextChunk(&blob) : split->NextRecord(&blob)) {
+      uint64_t len = blob.size;
+      if (mode == 1) len = std::strlen(static_cast<const char *>(blob.dptr));
+      if (total + len + 1 <= cap) {
+        std::memcpy(buf + total, blob.dptr, len);
+        if (mode == 1) buf[total + len] = '\n';
+      }
+      total += len + (mode == 1 ? 1 : 0);
+      ++n;
+    }
+    delete split;
+  } catch (const std::exception &e) {
+    Say(err, errlen, e.what());
+    return ~0ull;
+  }
+  if (pieces != NULL) *pieces = n;
+  return total;
+}
+
+}  // extern "C"

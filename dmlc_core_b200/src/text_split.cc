@@ -1,0 +1,291 @@
+#include "./text_split.h"
+
+#include <dirent.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <cerrno>
+#include <cstring>
+#include <regex>
+#include <thread>
+
+#include "./uri_spec.h"
+
+namespace dmlc {
+namespace b200 {
+
+namespace {
+inline bool IsEol(char c) { return c == '\n' || c == '\r'; }
+
+std::string StripProtocol(const std::string &p) {
+  if (p.compare(0, 7, "file://") == 0) return p.substr(7);
+  CHECK(p.find("://") == std::string::npos)
+      << "dmlc_core_b200 reads local files only, got " << p;
+  return p;
+}
+std::string StripTrailingSlash(std::string s) {
+  while (s.size() > 1 && s[s.size() - 1] == '/') s.resize(s.size() - 1);
+  return s;
+}
+}  // namespace
+
+TextSplit::TextSplit(const char *uri, unsigned part_index, unsigned num_parts)
+    : begin_(0), end_(0), cur_(0), read_threads_(1), chunk_size_hint_(8u << 20),
+      rec_pos_(0), rec_end_(0) {
+  unsigned hw = std::thread::hardware_concurrency();
+  read_threads_ = hw >= 16 ? 8 : (hw >= 4 ? static_cast<int>(hw / 2) : 1);
+  ExpandUri(uri);
+  CHECK_NE(files_.size(), 0U) << "Cannot find any files that matches the URI pattern " << uri;
+  start_.resize(files_.size() + 1);
+  start_[0] = 0;
+  for (size_t i = 0; i < files_.size(); ++i) start_[i + 1] = start_[i] + files_[i].size;
+  ResetPartition(part_index, num_parts);
+}
+
+TextSplit::~TextSplit() {
+  for (size_t i = 0; i < files_.size(); ++i) {
+    if (files_[i].fd >= 0) close(files_[i].fd);
+  }
+}
+
+/* One entry of the ';' list: a file, a directory (its non-empty regular files, listing order), or
+   a regular expression matched against the full paths inside its directory
+   (reference src/io/input_split_base.cc:96-175). */
+void TextSplit::ExpandUri(const std::string &uri) {
+  size_t pos = 0;
+  while (pos <= uri.size()) {
+    size_t semi = uri.find(';', pos);
+    if (semi == std::string::npos) semi = uri.size();
+    if (semi > pos) AddPath(StripProtocol(uri.substr(pos, semi - pos)), false);
+    pos = semi + 1;
+  }
+}
+
+void TextSplit::AddPath(const std::string &path, bool from_listing) {
+  struct stat sb;
+  if (stat(path.c_str(), &sb) == 0) {
+    if (S_ISDIR(sb.st_mode)) {
+      if (from_listing) return;  /* not recursive */
+      DIR *dir = opendir(path.c_str());
+      CHECK(dir != NULL) << "ListDirectory " << path << " error: " << strerror(errno);
+      struct dirent *ent;
+      while ((ent = readdir(dir)) != NULL) {
+        if (!strcmp(ent->d_name, ".") || !strcmp(ent->d_name, "..")) continue;
+        std::string child = path;
+        if (child[child.size() - 1] != '/') child += '/';
+        AddPath(child + ent->d_name, true);
+      }
+      closedir(dir);
+      return;
+    }
+    if (sb.st_size == 0) return;  /* empty files are dropped */
+    File f;
+    f.path = path;
+    f.size = static_cast<uint64_t>(sb.st_size);
+    f.fd = open(path.c_str(), O_RDONLY);
+    CHECK(f.fd >= 0) << "cannot open " << path << ": " << strerror(errno);
+    files_.push_back(f);
+    return;
+  }
+  if (from_listing) return;
+  /* not an existing path: treat the last component as a regex over its directory */
+  const size_t slash = path.rfind('/');
+  CHECK(slash != std::string::npos && slash + 1 != path.size())
+      << "LocalFileSystem.GetPathInfo: " << path << " error: " << strerror(ENOENT);
+  const std::string dirname = slash == 0 ? "/" : path.substr(0, slash);
+  DIR *dir = opendir(dirname.c_str());
+  CHECK(dir != NULL) << "ListDirectory " << dirname << " error: " << strerror(errno);
+  std::regex pattern;
+  try {
+    pattern = std::regex(path);
+  } catch (const std::regex_error &e) {
+    closedir(dir);
+    LOG(FATAL) << e.what() << " bad regex " << path;
+  }
+  struct dirent *ent;
+  while ((ent = readdir(dir)) != NULL) {
+    if (!strcmp(ent->d_name, ".") || !strcmp(ent->d_name, "..")) continue;
+    std::string child = dirname;
+    if (child[child.size() - 1] != '/') child += '/';
+    child += ent->d_name;
+    if (std::regex_match(StripTrailingSlash(child), pattern)) AddPath(child, true);
+  }
+  closedir(dir);
+}
+
+size_t TextSplit::GetTotalSize(void) { return static_cast<size_t>(start_.back()); }
+
+size_t TextSplit::FileAt(uint64_t offset) const {
+  /* upper_bound - 1 over the prefix sums, as src/io/input_split_base.cc:38-43 */
+  return static_cast<size_t>(std::upper_bound(start_.begin(), start_.end(), offset) -
+                             start_.begin()) - 1;
+}
+
+/* Bytes to skip from (file, offset) to the next record begin: through the first EOL and every
+   EOL byte directly after it, stopping at the end of that file (line_split.cc:9-26). */
+uint64_t TextSplit::SkipToRecordBegin(size_t file, uint64_t off) {
+  const File &f = files_[file];
+  char buf[4096];
+  uint64_t n = 0;
+  bool in_eol_run = false;
+  for (;;) {
+    const ssize_t got = pread(f.fd, buf, sizeof(buf), static_cast<off_t>(off + n));
+    if (got <= 0) return n;
+    for (ssize_t i = 0; i < got; ++i) {
+      if (!in_eol_run) {
+        ++n;
+        if (IsEol(buf[i])) in_eol_run = true;
+      } else {
+        if (!IsEol(buf[i])) return n;
+        ++n;
+      }
+    }
+  }
+}
+
+void TextSplit::ResetPartition(unsigned rank, unsigned nsplit) {
+  CHECK(rank < nsplit) << "invalid input parameter for InputSplit::Create";
+  const uint64_t total = start_.back();
+  const uint64_t step = (total + nsplit - 1) / nsplit;
+  begin_ = std::min<uint64_t>(step * rank, total);
+  end_ = std::min<uint64_t>(step * (rank + 1), total);
+  if (begin_ != end_) {
+    const size_t fe = FileAt(end_);
+    if (end_ != start_[fe]) end_ += SkipToRecordBegin(fe, end_ - start_[fe]);
+    const size_t fb = FileAt(begin_);
+    if (begin_ != start_[fb]) begin_ += SkipToRecordBegin(fb, begin_ - start_[fb]);
+  }
+  BeforeFirst();
+}
+
+void TextSplit::BeforeFirst(void) {
+  cur_ = begin_;
+  rec_pos_ = rec_end_ = 0;
+}
+
+void TextSplit::HintChunkSize(size_t chunk_size) {
+  chunk_size_hint_ = std::max(chunk_size_hint_, chunk_size);
+}
+
+void TextSplit::ReadRangeSerial(uint64_t offset, char *dst, size_t n) {
+  size_t f = FileAt(offset);
+  while (n != 0) {
+    CHECK(f < files_.size()) << "read past the end of the input files";
+    const uint64_t in_file = offset - start_[f];
+    const size_t want = static_cast<size_t>(std::min<uint64_t>(n, files_[f].size - in_file));
+    size_t done = 0;
+    while (done < want) {
+      const ssize_t got = pread(files_[f].fd, dst + done, want - done,
+                                static_cast<off_t>(in_file + done));
+      CHECK(got > 0) << "short read on " << files_[f].path << ": "
+                     << (got < 0 ? strerror(errno) : "file shrank");
+      done += static_cast<size_t>(got);
+    }
+    dst += want;
+    offset += want;
+    n -= want;
+    ++f;
+  }
+}
+
+void TextSplit::ReadRange(uint64_t offset, char *dst, size_t n) {
+  const size_t kMinPiece = 4u << 20;
+  int pieces = static_cast<int>(std::min<size_t>(read_threads_, (n + kMinPiece - 1) / kMinPiece));
+  if (pieces <= 1) {
+    ReadRangeSerial(offset, dst, n);
+    return;
+  }
+  const size_t per = ((n + pieces - 1) / pieces + 4095) / 4096 * 4096;
+  std::vector<std::thread> pool;
+  std::vector<std::string> errors(pieces);
+  for (int i = 0; i < pieces; ++i) {
+    const size_t lo = std::min(n, per * i), hi = std::min(n, per * (i + 1));
+    if (lo == hi) continue;
+    pool.push_back(std::thread([this, offset, dst, lo, hi, i, &errors]() {
+      try {
+        ReadRangeSerial(offset + lo, dst + lo, hi - lo);
+      } catch (const dmlc::Error &e) {
+        errors[i] = e.what();
+      }
+    }));
+  }
+  for (size_t i = 0; i < pool.size(); ++i) pool[i].join();
+  for (int i = 0; i < pieces; ++i) {
+    if (!errors[i].empty()) LOG(FATAL) << errors[i];
+  }
+}
+
+size_t TextSplit::ReadLines(void *buf, size_t cap) {
+  if (cur_ >= end_ || cap == 0) return 0;
+  char *dst = static_cast<char *>(buf);
+  const uint64_t left = end_ - cur_;
+  if (left <= cap) {
+    ReadRange(cur_, dst, static_cast<size_t>(left));
+    cur_ = end_;
+    return static_cast<size_t>(left);
+  }
+  ReadRange(cur_, dst, cap);
+  /* cut after the last EOL byte (FindLastRecordBegin, line_split.cc:27-34); the bytes behind
+     it are simply read again by the next call */
+  size_t cut = cap;
+  while (cut > 1 && !IsEol(dst[cut - 1])) --cut;
+  if (cut <= 1 && !IsEol(dst[0])) return kLineTooLong;
+  if (cut <= 1) cut = 1;
+  cur_ += cut;
+  return cut;
+}
+
+bool TextSplit::NextChunk(Blob *out_chunk) {
+  size_t cap = chunk_size_hint_;
+  for (;;) {
+    if (chunk_.size() < cap + 1) chunk_.resize(cap + 1);
+    const size_t n = ReadLines(chunk_.data(), cap);
+    if (n == kLineTooLong) {
+      cap *= 2;  /* one line longer than the buffer: grow, like Chunk::Load (:249-251) */
+      continue;
+    }
+    if (n == 0) return false;
+    chunk_[n] = '\0';
+    out_chunk->dptr = chunk_.data();
+    out_chunk->size = n;
+    rec_pos_ = rec_end_ = 0;
+    return true;
+  }
+}
+
+bool TextSplit::NextRecord(Blob *out_rec) {
+  /* records are served out of chunks (reference LineSplitter::ExtractNextRecord,
+     src/io/line_split.cc:36-55): a record is the line plus the EOL run that follows it; the last
+     byte of that run (or the byte after the chunk) is overwritten by NUL */
+  while (rec_pos_ == rec_end_) {
+    Blob chunk;
+    if (!NextChunk(&chunk)) return false;
+    rec_pos_ = 0;
+    rec_end_ = chunk.size;
+  }
+  char *base = chunk_.data();
+  size_t p = rec_pos_;
+  while (p != rec_end_ && !IsEol(base[p])) ++p;
+  while (p != rec_end_ && IsEol(base[p])) ++p;
+  if (p == rec_end_) base[p] = '\0'; else base[p - 1] = '\0';
+  out_rec->dptr = base + rec_pos_;
+  out_rec->size = p - rec_pos_;
+  rec_pos_ = p;
+  return true;
+}
+
+}  // namespace b200
+
+InputSplit *InputSplit::Create(const char *uri, unsigned part_index, unsigned num_parts,
+                               const char *type) {
+  b200::UriSpec spec(uri, part_index, num_parts);
+  CHECK(part_index < num_parts) << "invalid input parameter for InputSplit::Create";
+  CHECK(!strcmp(type, "text")) << "unknown input split type " << type
+                               << " (dmlc_core_b200 provides the \"text\" split only)";
+  CHECK(spec.cache_file.empty()) << "#cachefile splits are not provided by dmlc_core_b200";
+  return new b200::TextSplit(spec.uri.c_str(), part_index, num_parts);
+}
+
+}  // namespace dmlc

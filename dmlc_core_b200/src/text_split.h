@@ -1,0 +1,80 @@
+/*
+ * TextSplit: the "text" InputSplit for local files, built for feeding a GPU.
+ *
+ * Partition semantics are the reference's (InputSplitBase::Init/ResetPartition,
+ * src/io/input_split_base.cc:13-64; LineSplitter::SeekRecordBegin / FindLastRecordBegin,
+ * src/io/line_split.cc:9-34): the files behind the URI form one logical byte stream of length T;
+ * part k of n is [ceil(T/n)*k, ceil(T/n)*(k+1)) with each end that is not a file start moved
+ * forward past the next end-of-line run; chunks are cut after the last EOL that fits.
+ *
+ * What differs is the mechanics: files are read with positional reads (pread) fanned out over a
+ * few threads, straight into a buffer the caller names -- the GPU parser passes the pinned
+ * staging buffer of its next pipeline slot -- so there is no fread-into-vector plus overflow
+ * memcpy (src/io/input_split_base.cc:211-258) and no prefetch thread
+ * (src/io/threaded_input_split.h:29-42) between the page cache and the DMA engine.
+ */
+#ifndef DMLC_CORE_B200_TEXT_SPLIT_H_
+#define DMLC_CORE_B200_TEXT_SPLIT_H_
+
+#include <dmlc/io.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace dmlc {
+namespace b200 {
+
+class TextSplit : public InputSplit {
+ public:
+  static const size_t kLineTooLong = static_cast<size_t>(-1);
+
+  TextSplit(const char *uri, unsigned part_index, unsigned num_parts);
+  virtual ~TextSplit();
+
+  virtual void HintChunkSize(size_t chunk_size);
+  virtual size_t GetTotalSize(void);
+  virtual void BeforeFirst(void);
+  virtual bool NextRecord(Blob *out_rec);
+  virtual bool NextChunk(Blob *out_chunk);
+  virtual void ResetPartition(unsigned part_index, unsigned num_parts);
+
+  /*
+   * Fill `buf` (capacity `cap`) with the next run of whole lines of this partition.
+   * Returns the number of bytes (0 at the end of the partition) or kLineTooLong when not even
+   * one line fits in `cap` (nothing consumed; retry with a larger buffer).
+   */
+  size_t ReadLines(void *buf, size_t cap);
+
+  /* adjusted byte range of the partition within the logical stream */
+  uint64_t PartitionBegin() const { return begin_; }
+  uint64_t PartitionEnd() const { return end_; }
+  /* threads used for one ReadLines call */
+  void SetReadThreads(int n) { read_threads_ = n < 1 ? 1 : n; }
+
+ private:
+  struct File {
+    std::string path;
+    uint64_t size;
+    int fd;
+  };
+  void ExpandUri(const std::string &uri);
+  void AddPath(const std::string &path, bool from_listing);
+  size_t FileAt(uint64_t offset) const;            /* last file whose start <= offset */
+  uint64_t SkipToRecordBegin(size_t file, uint64_t offset_in_file);
+  void ReadRange(uint64_t offset, char *dst, size_t n);      /* across files, multi-threaded */
+  void ReadRangeSerial(uint64_t offset, char *dst, size_t n);
+
+  std::vector<File> files_;
+  std::vector<uint64_t> start_;   /* start_[i] = stream offset of file i; start_[n] = T */
+  uint64_t begin_, end_, cur_;
+  int read_threads_;
+  /* NextChunk / NextRecord state */
+  std::vector<char> chunk_;
+  size_t chunk_size_hint_;
+  size_t rec_pos_, rec_end_;
+};
+
+}  // namespace b200
+}  // namespace dmlc
+#endif  // DMLC_CORE_B200_TEXT_SPLIT_H_

@@ -1,0 +1,146 @@
+"""GPU suite for the C++ drop-in: dmlc::Parser<IndexType>::Create(uri, part_index, num_parts,
+type) -> Next()/Value() over files, against the golden RowBlocks the unmodified reference
+produced through the same call, and against the reference itself when oracle/_ref travelled."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, golden_cases, load_golden
+from oracle.pyoracle import same_rowblocks
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def hostapi(cuda_lib):
+    from dmlc_core_b200 import build
+    build.build_host()
+    from dmlc_core_b200 import hostapi as h
+    h.load()
+    return h
+
+
+def _uri(path, fmt, lc):
+    return path + ("?format=csv&label_column=%d" % lc if fmt == "csv" else "")
+
+
+@pytest.mark.parametrize("case", golden_cases(), ids=lambda c: c["name"])
+def test_create_next_value_matches_golden(hostapi, case):
+    _, exp = load_golden(case)
+    path = os.path.join(GOLDEN, case["name"] + ".txt")
+    uri = _uri(path, case["format"], case["label_column"])
+    try:
+        p = hostapi.CppParser(uri, 0, 1, case["format"], case["index_bytes"])
+        got, _ = p.drain()
+        assert p.bytes_read() == os.path.getsize(path)
+        p.close()
+    except hostapi.DmlcError as e:
+        got = {"error": 1, "errmsg": str(e)}
+    assert same_rowblocks(got, exp) is None, case["name"]
+
+
+@pytest.mark.parametrize("kind,fmt,ib,lc", [("libsvm", "libsvm", 4, -1), ("csv", "csv", 4, 0),
+                                            ("libfm", "libfm", 8, -1), ("libsvm_qid", "libsvm", 4, -1),
+                                            ("criteo", "libsvm", 8, -1)])
+def test_sharded_parse_matches_oracle(hostapi, oracle, tmp_path, monkeypatch, kind, fmt, ib, lc):
+    """part_index / num_parts sharding (BASELINE configs 4-5): every part equals the oracle on
+    that part's bytes; the parts together are the whole file; BytesRead() ends at the part's
+    length; a second pass after BeforeFirst() repeats the first; small chunks force many blocks."""
+    from dmlc_core_b200 import datagen
+    monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
+    data, rows = datagen.generate(kind, 8, 5 << 20)
+    a, b = tmp_path / "a.txt", tmp_path / "b.txt"
+    cut = data.tobytes().index(b"\n", data.size // 3) + 1
+    a.write_bytes(data.tobytes()[:cut])
+    b.write_bytes(data.tobytes()[cut:])
+    uri = _uri(str(a) + ";" + str(b), fmt, lc)
+    total_rows = 0
+    for nparts in (1, 3):
+        labels = []
+        for part in range(nparts):
+            exp = oracle.parse_files(fmt, [str(a), str(b)], part, nparts, ib, lc)
+            p = hostapi.CppParser(uri, part, nparts, fmt, ib)
+            got, nblocks = p.drain()
+            assert same_rowblocks(got, exp) is None, (kind, nparts, part)
+            part_bytes, _, _ = oracle.split_bytes([str(a), str(b)], part, nparts)
+            assert p.bytes_read() == len(part_bytes)
+            if nparts == 1:
+                assert nblocks >= 4
+            p.before_first()
+            again, _ = p.drain()
+            assert same_rowblocks(again, exp) is None
+            assert p.bytes_read() == 2 * len(part_bytes)   # not reset, like the reference
+            p.close()
+            labels.append(got["label"])
+        assert sum(len(x) for x in labels) == rows
+
+
+def test_against_reference_parser_directly(hostapi, reference, tmp_path):
+    """Same URI, same (part, nparts) through both Parser::Create implementations."""
+    from dmlc_core_b200 import datagen
+    for kind, fmt, ib, lc in (("libsvm", "libsvm", 4, -1), ("csv", "csv", 4, 0), ("libfm", "libfm", 4, -1)):
+        data, _ = datagen.generate(kind, 12, 2 << 20)
+        f = tmp_path / (kind + ".txt")
+        f.write_bytes(data.tobytes())
+        uri = _uri(str(f), fmt, lc)
+        for part, nparts in ((0, 1), (1, 2), (3, 4)):
+            ref = reference.parse_uri(uri, part, nparts, fmt, ib)
+            p = hostapi.CppParser(uri, part, nparts, fmt, ib)
+            got, _ = p.drain()
+            p.close()
+            assert same_rowblocks(got, ref) is None, (kind, part, nparts)
+
+
+def test_row_block_iter_numcol(hostapi, oracle, tmp_path):
+    from dmlc_core_b200 import datagen
+    data, rows = datagen.generate("libsvm", 4, 1 << 20)
+    f = tmp_path / "it.svm"
+    f.write_bytes(data.tobytes())
+    exp = oracle.parse_buffer("libsvm", data.tobytes(), 4)
+    got, ncol = hostapi.row_iter(str(f), 0, 1, "libsvm", 4)
+    assert same_rowblocks(got, exp) is None
+    assert ncol == int(exp["index"].max()) + 1
+
+
+def test_long_line_and_error_propagation(hostapi, oracle, tmp_path, monkeypatch):
+    monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
+    # one line of ~3 MiB (longer than the 1 MiB staging buffer), then normal lines
+    line = b"1 " + b" ".join(b"%d:0.5" % i for i in range(1, 330000)) + b"\n"
+    text = line + b"0 1:2 3:4\n" * 1000
+    f = tmp_path / "long.svm"
+    f.write_bytes(text)
+    exp = oracle.parse_buffer("libsvm", text, 4)
+    p = hostapi.CppParser(str(f), 0, 1, "libsvm", 4)
+    got, _ = p.drain()
+    p.close()
+    assert same_rowblocks(got, exp) is None
+    bad = tmp_path / "bad.svm"
+    bad.write_bytes(b"1 1:1\n0 -2:1\n")
+    p = hostapi.CppParser(str(bad), 0, 1, "libsvm", 4)
+    with pytest.raises(hostapi.DmlcError, match="sign == true"):
+        p.drain()
+    p.close()
+
+
+def test_true_dropin_build_against_reference_headers(hostapi):
+    """oracle/_ref/libdmlc_dropin.so = the reference's headers, InputSplit, filesystem and
+    registry with src/data.cc replaced by this package's parser.
+    Built only where /root/reference exists; it travels to the GPU box like libdmlc_ref.so."""
+    from conftest import ROOT
+    path = os.path.join(ROOT, "oracle", "_ref", "libdmlc_dropin.so")
+    if not os.path.exists(path):
+        pytest.skip("drop-in build not present")
+    lib = hostapi.load(path)
+    for case in golden_cases():
+        _, exp = load_golden(case)
+        f = os.path.join(GOLDEN, case["name"] + ".txt")
+        try:
+            p = hostapi.CppParser(_uri(f, case["format"], case["label_column"]), 0, 1,
+                                  case["format"], case["index_bytes"], lib=lib)
+            got, _ = p.drain()
+            assert p.bytes_read() == os.path.getsize(f)
+            p.close()
+        except hostapi.DmlcError as e:
+            got = {"error": 1, "errmsg": str(e)}
+        assert same_rowblocks(got, exp) is None, case["name"]

@@ -1,0 +1,102 @@
+"""CPU suite for the C++ host layer (dmlc_core_b200/src): InputSplit partition arithmetic against
+the compiled reference, URI handling and error behaviour.  No GPU work happens here."""
+import os
+import random
+
+import pytest
+
+
+@pytest.fixture(scope="module")
+def hostapi():
+    from dmlc_core_b200 import build
+    build.build_cuda()
+    build.build_host()
+    from dmlc_core_b200 import hostapi as h
+    h.load()
+    return h
+
+
+def _files(tmp_path, rnd, nfiles, eol_choices):
+    paths = []
+    for i in range(nfiles):
+        lines = []
+        for _ in range(rnd.randint(3, 80)):
+            lines.append(" ".join("%d:%d" % (rnd.randint(1, 999), rnd.randint(0, 9))
+                                  for _ in range(rnd.randint(0, 12))) + rnd.choice(eol_choices))
+        p = tmp_path / ("f%02d.txt" % i)
+        p.write_bytes(("1 " + "0 ".join(lines)).encode())
+        paths.append(str(p))
+    return paths
+
+
+def test_partitions_match_reference(hostapi, reference, tmp_path):
+    """InputSplit::Create(uri, k, n, "text") yields exactly the bytes the reference yields
+    (ResetPartition / SeekRecordBegin semantics), for single files, ';' lists, CRLF, blank lines,
+    tiny chunk hints, more parts than lines."""
+    rnd = random.Random(17)
+    for trial, (nfiles, eols) in enumerate([(1, ["\n"]), (3, ["\n", "\r\n", "\n\n"]), (4, ["\r"]),
+                                            (2, ["\n", "\n\n\n"])]):
+        d = tmp_path / ("t%d" % trial)
+        d.mkdir()
+        paths = _files(d, rnd, nfiles, eols)
+        uri = ";".join(paths)
+        total = sum(os.path.getsize(p) for p in paths)
+        for nparts in (1, 2, 3, 7, 16, 200):
+            joined = b""
+            for part in range(nparts):
+                want, n, _ = reference.split_bytes(uri, part, nparts, total + 64)
+                got, _ = hostapi.split_bytes(uri, part, nparts, mode=0, cap=total + 64)
+                assert got == want, (trial, nparts, part)
+                joined += got
+            assert len(joined) == total
+
+
+def test_chunks_are_line_aligned_and_records_complete(hostapi, tmp_path):
+    from dmlc_core_b200 import datagen
+    data, rows = datagen.generate("libsvm", 9, 9 << 20)
+    p = tmp_path / "big.svm"
+    p.write_bytes(data.tobytes())
+    got, pieces = hostapi.split_bytes(str(p), 0, 1, mode=0, cap=data.size + 64)
+    assert got == data.tobytes() and pieces >= 2       # default 8 MiB chunks
+    recs, nrec = hostapi.split_bytes(str(p), 1, 3, mode=1, cap=data.size + 64)
+    part, _ = hostapi.split_bytes(str(p), 1, 3, mode=0, cap=data.size + 64)
+    # (the last record of a chunk keeps its EOL byte, as in the reference's ExtractNextRecord)
+    assert [r for r in recs.split(b"\n") if r] == [r for r in part.split(b"\n") if r]
+    assert nrec == part.count(b"\n")
+
+
+def test_directory_and_regex_uris(hostapi, tmp_path):
+    d = tmp_path / "dir"
+    d.mkdir()
+    for name, body in (("a.svm", b"1 1:1\n"), ("b.svm", b"0 2:2\n"), ("c.txt", b"1 3:3\n"), ("empty.svm", b"")):
+        (d / name).write_bytes(body)
+    whole, _ = hostapi.split_bytes(str(d), 0, 1)
+    assert sorted(whole.split(b"\n")[:-1]) == [b"0 2:2", b"1 1:1", b"1 3:3"]
+    only, _ = hostapi.split_bytes(str(d) + "/.*\\.svm", 0, 1)
+    assert sorted(only.split(b"\n")[:-1]) == [b"0 2:2", b"1 1:1"]
+    with pytest.raises(hostapi.DmlcError):
+        hostapi.split_bytes(str(d) + "/nothing_here", 0, 1)
+    with pytest.raises(hostapi.DmlcError):
+        hostapi.split_bytes(str(d / "a.svm"), 3, 3)        # part_index must be < num_parts
+
+
+def test_create_errors_match_reference_behaviour(hostapi, tmp_path):
+    """Unknown types, csv with a 64-bit index, bad csv arguments: all raise (reference
+    src/data.cc:80-82,158; csv_parser.h:50-51). On a box without a GPU a valid Create raises too
+    -- the product has no CPU path."""
+    import torch
+    f = tmp_path / "x.csv"
+    f.write_bytes(b"1,2,3\n")
+    with pytest.raises(hostapi.DmlcError, match="Unknown data type"):
+        hostapi.CppParser(str(f), 0, 1, "parquet")
+    with pytest.raises(hostapi.DmlcError, match="Unknown data type csv"):
+        hostapi.CppParser(str(f) + "?format=csv", 0, 1, "auto", index_bytes=8)
+    with pytest.raises(hostapi.DmlcError, match="Cannot find argument"):
+        hostapi.CppParser(str(f) + "?format=csv&delimiter=;", 0, 1, "csv")
+    with pytest.raises(hostapi.DmlcError):
+        hostapi.CppParser(str(f) + "?format=csv&label_column=x", 0, 1, "csv")
+    with pytest.raises(hostapi.DmlcError):
+        hostapi.CppParser(str(f) + "#a#b", 0, 1, "csv")
+    if not torch.cuda.is_available():
+        with pytest.raises(hostapi.DmlcError, match="no CPU path|cannot create"):
+            hostapi.CppParser(str(f) + "?format=csv&label_column=0", 0, 1, "auto")
