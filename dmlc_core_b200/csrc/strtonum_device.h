@@ -234,5 +234,238 @@ B200P_HD uint64_t ToQid(const Text &t, uint32_t p) {
   return negative ? (0ull - v) : v;
 }
 
+
+/* ------------------------------------------------------------------------------------------
+ * Register-window fast paths.
+ *
+ * The general converters above fetch one byte per loop trip. Almost every real token is short
+ * and plain ("-7.60915", "0.137604", "52172", "1"), so the fast paths pull 16 bytes of the
+ * token into registers with three aligned 8-byte loads, find the digit runs with SWAR
+ * arithmetic, and convert from registers.  Anything they cannot prove identical to the general
+ * code -- leading whitespace, > 7 integer digits (fp32 accumulation starts rounding at 2^24),
+ * > 7 fraction digits, an exponent, a token that does not end inside the window, a window
+ * that would read past the chunk -- is handed to the general code.
+ *
+ * Fraction: the reference computes float(double(digits) / double(10^k)).  For k <= 9 and every
+ * digits < 10^k, float(double(digits) * RN(10^-k)) is the same fp32 value; that was checked
+ * exhaustively on the CPU (all 1 111 111 111 cases), so one DMUL replaces the
+ * IEEE fp64 division.
+ * ------------------------------------------------------------------------------------------ */
+#if defined(__CUDA_ARCH__)
+B200P_D void Load8(const uint8_t *p, uint32_t *lo, uint32_t *hi) {
+  const uint2 v = __ldg(reinterpret_cast<const uint2 *>(p));
+  *lo = v.x;
+  *hi = v.y;
+}
+/* bytes k.. of the 8-byte pair (hi:lo), k = 0..3 */
+B200P_D uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) { return __funnelshift_r(lo, hi, k * 8u); }
+B200P_D int FirstSet(uint32_t x) { return __ffs(static_cast<int>(x)) - 1; }
+B200P_D float U32ToFloat(uint32_t x) { return __uint2float_rn(x); }
+B200P_D float Fraction8(uint32_t f8) {
+  return __double2float_rn(__dmul_rn(__uint2double_rn(f8), 1e-8));
+}
+#else
+inline void Load8(const uint8_t *p, uint32_t *lo, uint32_t *hi) {
+  uint32_t a = 0, b = 0;
+  for (int i = 0; i < 4; ++i) {
+    a |= static_cast<uint32_t>(p[i]) << (8 * i);
+    b |= static_cast<uint32_t>(p[i + 4]) << (8 * i);
+  }
+  *lo = a;
+  *hi = b;
+}
+inline uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) {
+  return k == 0u ? lo : ((lo >> (8u * k)) | (hi << (32u - 8u * k)));
+}
+inline int FirstSet(uint32_t x) { return __builtin_ffs(static_cast<int>(x)) - 1; }
+inline float U32ToFloat(uint32_t x) { return static_cast<float>(x); }
+inline float Fraction8(uint32_t f8) {
+  volatile double q = static_cast<double>(f8) * 1e-8;
+  return static_cast<float>(q);
+}
+#endif
+
+/* 16 bytes of text starting at p, as four little-endian words */
+struct Window {
+  uint32_t x0, x1, x2, x3;
+};
+
+/* false if the aligned loads would touch memory past the chunk
+   ([p & ~7, (p & ~7) + 24) must be readable) */
+B200P_HD bool LoadWindow(const Text &t, uint32_t p, Window *w) {
+  const uint32_t a = p & ~7u;
+  if (a + 24u > t.size) return false;
+  uint32_t w0, w1, w2, w3, w4, w5;
+  Load8(t.data + a, &w0, &w1);
+  Load8(t.data + a + 8, &w2, &w3);
+  Load8(t.data + a + 16, &w4, &w5);
+  if ((p & 4u) != 0u) {
+    w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5;
+  }
+  const uint32_t k = p & 3u;
+  w->x0 = BytesFrom(w0, w1, k);
+  w->x1 = BytesFrom(w1, w2, k);
+  w->x2 = BytesFrom(w2, w3, k);
+  w->x3 = BytesFrom(w3, w4, k);
+  return true;
+}
+
+/* bit 7 of every byte that is NOT an ASCII digit */
+B200P_HD uint32_t NonDigitFlags(uint32_t x) {
+  const uint32_t y = x ^ 0x30303030u;
+  return (((y & 0x7f7f7f7fu) + 0x76767676u) | y) & 0x80808080u;
+}
+
+/* byte i (0..7) of the pair (hi:lo) */
+B200P_HD uint32_t ByteOf(uint32_t lo, uint32_t hi, uint32_t i) {
+  return ((i < 4u ? lo : hi) >> ((i & 3u) * 8u)) & 0xffu;
+}
+
+/* four digit values d0 d1 d2 d3 (one per byte, d0 in the low byte = most significant) -> number */
+B200P_HD uint32_t Pack4(uint32_t z) {
+  const uint32_t t = (z * 10u + (z >> 8)) & 0x00ff00ffu; /* d0d1 | d2d3 << 16 */
+  return (t & 0xffffu) * 100u + (t >> 16);
+}
+
+B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
+  Window w;
+  if (!LoadWindow(t, p, &w)) return false;
+  const uint32_t c0 = w.x0 & 0xffu;
+  if (c0 <= 0x20u) return false;           /* whitespace / control first: general code */
+  const bool negative = c0 == '-';
+  uint32_t used = 0;                        /* window bytes consumed so far */
+  if (negative || c0 == '+') {
+    w.x0 = BytesFrom(w.x0, w.x1, 1u);
+    w.x1 = BytesFrom(w.x1, w.x2, 1u);
+    w.x2 = BytesFrom(w.x2, w.x3, 1u);
+    w.x3 >>= 8;
+    used = 1;
+  }
+  /* integer digits: at most 7, so that the reference's fp32 accumulation is exact (< 2^24) */
+  const uint32_t nd0 = NonDigitFlags(w.x0), nd1 = NonDigitFlags(w.x1);
+  uint32_t n1;
+  if (nd0 != 0u) {
+    n1 = static_cast<uint32_t>(FirstSet(nd0)) >> 3;
+  } else if (nd1 != 0u) {
+    n1 = 4u + (static_cast<uint32_t>(FirstSet(nd1)) >> 3);
+  } else {
+    return false;
+  }
+  uint32_t term = ByteOf(w.x0, w.x1, n1);
+  const uint32_t y0 = w.x0 & 0x0f0f0f0fu, y1 = w.x1 & 0x0f0f0f0fu;
+  uint32_t ip = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (uint32_t i = 0; i < 7u; ++i) {
+    const uint32_t d = ((i < 4u ? y0 : y1) >> ((i & 3u) * 8u)) & 0xffu;
+    if (i < n1) ip = ip * 10u + d;
+  }
+  float v = U32ToFloat(ip);
+  used += n1;
+  if (term == '.') {
+    /* fraction: the 8 bytes after the dot, digits beyond the run zeroed = the digits right-padded
+       to 8 places; float(double(F8) * 1e-8) == float(double(f) / double(10^k)) for every k <= 8
+       (exhaustive CPU check) */
+    const uint32_t f0 = n1 + 1u;            /* 1 .. 8 */
+    uint32_t a, b, c;
+    if (f0 < 4u) {
+      a = w.x0; b = w.x1; c = w.x2;
+    } else if (f0 < 8u) {
+      a = w.x1; b = w.x2; c = w.x3;
+    } else {
+      a = w.x2; b = w.x3; c = 0u;
+    }
+    const uint32_t r0 = BytesFrom(a, b, f0 & 3u), r1 = BytesFrom(b, c, f0 & 3u);
+    const uint32_t ndr0 = NonDigitFlags(r0), ndr1 = NonDigitFlags(r1);
+    uint32_t n2, m0, m1;
+    if (ndr0 != 0u) {
+      const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr0)) & ~7u;
+      n2 = bit >> 3;
+      m0 = (1u << bit) - 1u;
+      m1 = 0u;
+    } else if (ndr1 != 0u) {
+      const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr1)) & ~7u;
+      n2 = 4u + (bit >> 3);
+      m0 = 0xffffffffu;
+      m1 = (1u << bit) - 1u;
+    } else {
+      return false;                          /* >= 8 fraction digits */
+    }
+    used += 1u + n2;
+    if (used > 15u) return false;            /* the terminator must be a real byte of the window */
+    term = ByteOf(r0, r1, n2);
+    const uint32_t f8 = Pack4(r0 & 0x0f0f0f0fu & m0) * 10000u + Pack4(r1 & 0x0f0f0f0fu & m1);
+    v = AddRn(v, Fraction8(f8));
+  }
+  if ((term | 0x20u) == 'e') return false;   /* exponent: general code */
+  *out = negative ? -v : v;
+  return true;
+}
+
+/* float token at p: window fast path, else the general converter */
+B200P_HD float ToFloatFast(const Text &t, uint32_t p) {
+  float v;
+  if (ToFloatWindow(t, p, &v)) return v;
+  return ToFloat(t, p, 0);
+}
+
+/* unsigned token at p: 1..15 digits followed by a non-digit inside the window */
+template <bool WIDE>
+B200P_HD bool ToUintWindow(const Text &t, uint32_t p, uint64_t *out) {
+  Window w;
+  if (!LoadWindow(t, p, &w)) return false;
+  const uint32_t nd0 = NonDigitFlags(w.x0);
+  uint32_t n;
+  if (nd0 != 0u) {
+    n = static_cast<uint32_t>(FirstSet(nd0)) >> 3;
+    if (n == 0u) return false;              /* sign, whitespace, empty: general code */
+  } else {
+    const uint32_t nd1 = NonDigitFlags(w.x1);
+    if (nd1 != 0u) {
+      n = 4u + (static_cast<uint32_t>(FirstSet(nd1)) >> 3);
+    } else {
+      const uint32_t nd2 = NonDigitFlags(w.x2);
+      if (nd2 != 0u) {
+        n = 8u + (static_cast<uint32_t>(FirstSet(nd2)) >> 3);
+      } else {
+        const uint32_t nd3 = NonDigitFlags(w.x3);
+        if (nd3 == 0u) return false;        /* >= 16 digits */
+        n = 12u + (static_cast<uint32_t>(FirstSet(nd3)) >> 3);
+      }
+    }
+  }
+  const uint32_t y[4] = {w.x0 & 0x0f0f0f0fu, w.x1 & 0x0f0f0f0fu, w.x2 & 0x0f0f0f0fu,
+                         w.x3 & 0x0f0f0f0fu};
+  /* digits wrap modulo 2^32 / 2^64 exactly like the sequential accumulation */
+  if (WIDE) {
+    uint64_t v = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (uint32_t i = 0; i < 15u; ++i) {
+      if (i < n) v = v * 10ull + ((y[i >> 2] >> ((i & 3u) * 8u)) & 0xffu);
+    }
+    *out = v;
+  } else {
+    uint32_t v = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (uint32_t i = 0; i < 15u; ++i) {
+      if (i < n) v = v * 10u + ((y[i >> 2] >> ((i & 3u) * 8u)) & 0xffu);
+    }
+    *out = v;
+  }
+  return true;
+}
+
+template <bool WIDE>
+B200P_HD uint64_t ToUintFast(const Text &t, uint32_t p, bool *negative) {
+  uint64_t v;
+  if (ToUintWindow<WIDE>(t, p, &v)) return v;
+  return ToUint<WIDE>(t, p, negative);
+}
+
 }  // namespace b200p
 #endif  // DMLC_CORE_B200_STRTONUM_DEVICE_H_

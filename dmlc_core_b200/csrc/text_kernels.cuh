@@ -136,6 +136,34 @@ __device__ __forceinline__ Masks16 Classify(const uint4 v) {
   return m;
 }
 
+/* Class flags of 16 bytes, one word at a time, bit 7 of each byte (no bit gathering):
+   fa = digit-run bytes (LibSVM/LibFM) or separators ',' | EOL (CSV); fe = EOL bytes. */
+template <int FMT>
+__device__ __forceinline__ void ClassifyFlags(const uint4 v, uint32_t (&fa)[4], uint32_t (&fe)[4]) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t xm = w[i] & 0x7f7f7f7fu;
+    const uint32_t not_lf = (xm ^ 0x0a0a0a0au) + 0x7f7f7f7fu;   /* bit 7 clear iff '\n' */
+    const uint32_t not_cr = (xm ^ 0x0d0d0d0du) + 0x7f7f7f7fu;
+    fe[i] = ~(not_lf & not_cr) & ~w[i] & 0x80808080u;
+    if (FMT == kCSV) {
+      const uint32_t not_comma = (xm ^ 0x2c2c2c2cu) + 0x7f7f7f7fu;
+      fa[i] = ~(not_lf & not_cr & not_comma) & ~w[i] & 0x80808080u;
+    } else {
+      fa[i] = WordDigitChar(w[i]) & 0x80808080u;
+    }
+  }
+}
+
+/* 16-bit byte mask -> four words with bit 7 of each selected byte set */
+__device__ __forceinline__ void ExpandMask(uint32_t mask16, uint32_t (&out)[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    out[i] = ((((mask16 >> (4 * i)) & 0xfu) * 0x00204081u) & 0x01010101u) << 7;
+  }
+}
+
 /* 16 bytes at `pos` (multiple of 16); bytes at or past `size` read as NUL */
 __device__ __forceinline__ uint4 Load16(const uint8_t *text, uint32_t size, uint32_t pos) {
   if (pos + 16u <= size) {
@@ -249,13 +277,13 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
   const uint32_t need = flush ? 1u : 32u;
   while (st.n_label >= need) {
     const uint32_t take = min(st.n_label, 32u);
-    if (lane < take) prm.label[st.w_label + lane] = ToFloat(txt, ws.q_label[lane], 0);
+    if (lane < take) prm.label[st.w_label + lane] = ToFloatFast(txt, ws.q_label[lane]);
     st.w_label += take;
     QueuePop(ws.q_label, st.n_label, take, lane);
   }
   while (st.n_weight >= need) {
     const uint32_t take = min(st.n_weight, 32u);
-    if (lane < take) prm.weight[st.w_weight + lane] = ToFloat(txt, ws.q_weight[lane], 0);
+    if (lane < take) prm.weight[st.w_weight + lane] = ToFloatFast(txt, ws.q_weight[lane]);
     st.w_weight += take;
     QueuePop(ws.q_weight, st.n_weight, take, lane);
   }
@@ -272,10 +300,10 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
     bool neg = false;
     if (lane < take) {
       StoreIdx<IdxT>(prm.index, st.w_index + lane,
-                     ToUint<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg));
+                     ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg));
       if (FMT == kLibFM) {
         StoreIdx<IdxT>(prm.field, st.w_index + lane,
-                       ToUint<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg));
+                       ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg));
       }
     }
     if (neg) st.error |= kErrNegativeIndex; /* lane-local; OR-reduced at the end of the walk */
@@ -288,7 +316,7 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
   }
   while (st.n_value >= need) {
     const uint32_t take = min(st.n_value, 32u);
-    if (lane < take) prm.value[st.w_value + lane] = ToFloat(txt, ws.q_value[lane], 0);
+    if (lane < take) prm.value[st.w_value + lane] = ToFloatFast(txt, ws.q_value[lane]);
     st.w_value += take;
     QueuePop(ws.q_value, st.n_value, take, lane);
   }
@@ -489,7 +517,7 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
           static_cast<unsigned long long>(st.seen[kNnz] + __popc(m_value & lt));
     }
     if (active) {
-      const float v = ToFloat(txt, at, 0);
+      const float v = ToFloatFast(txt, at);
       if (is_label) {
         prm.label[row] = v;
       } else {
@@ -567,67 +595,111 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   if (begin < hi) {
     uint32_t fill = 0;          /* tokens waiting in ws.tokens */
     uint32_t end = prm.size;    /* tightened once the closing EOL is seen */
-    uint32_t prev_a = 0;        /* LibSVM/LibFM: last byte of previous lane/step was in a run.
-                                   CSV: last byte was a comma */
-    uint32_t prev_eol = 1;      /* CSV: last byte was an EOL (a line starts at `begin`) */
+    /* class flags of the last 4 bytes of the previous step (only the top byte's flag is used):
+       LibSVM/LibFM: byte was part of a digit run; CSV: byte was a comma or an EOL */
+    uint32_t carry_a = FMT == kCSV ? 0x80000000u : 0u; /* the EOL before `begin` is a separator */
+    uint32_t carry_e = 0x80000000u; /* CSV: an EOL precedes `begin` (a line starts there) */
     bool done = false;
+    uint32_t csv_fields = 0, csv_rows = 0; /* per-lane tallies of the CSV counting shortcut */
     for (uint32_t base = begin & ~uint32_t(kStepBytes - 1); !done; base += kStepBytes) {
       const uint32_t first_byte = base + 16u * lane;
-      const uint4 v = Load16(prm.text, prm.size, first_byte);
-      const Masks16 raw = Classify<FMT>(v); /* bytes past the chunk load as NUL: no class */
-      /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
-      {
-        const uint32_t closing = raw.eol & KeepMask(first_byte, hi - 1u, prm.size);
-        const uint32_t who = __ballot_sync(0xffffffffu, closing != 0u);
+      /* interior step: wholly owned, wholly inside the chunk, and too early to hold the EOL
+         that closes the region -- no masks, no bounds checks (the common case: 14 of 16 steps
+         of an 8 KiB range) */
+      const bool interior = base >= begin && base + kStepBytes <= hi - 1u;
+      uint32_t fa[4], fe[4];    /* per-word class flags, bit 7 of each byte */
+      uint32_t keep[4];
+      if (interior) {
+        ClassifyFlags<FMT>(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), fa, fe);
+      } else {
+        ClassifyFlags<FMT>(Load16(prm.text, prm.size, first_byte), fa, fe);
+        /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
+        uint32_t closing[4];
+        ExpandMask(KeepMask(first_byte, hi - 1u, prm.size), closing);
+        uint32_t mine = 0xffffffffu; /* byte offset of my first closing EOL */
+#pragma unroll
+        for (int i = 3; i >= 0; --i) {
+          const uint32_t c = fe[i] & closing[i];
+          if (c != 0u) mine = 4u * i + ((__ffs(c) - 1) >> 3);
+        }
+        const uint32_t who = __ballot_sync(0xffffffffu, mine != 0xffffffffu);
         if (who != 0u) {
           const int src = __ffs(who) - 1;
-          const uint32_t es = __shfl_sync(0xffffffffu, closing, src);
-          end = base + 16u * src + (__ffs(es) - 1) + 1u;
+          end = base + 16u * src + __shfl_sync(0xffffffffu, mine, src) + 1u;
           done = true;
         } else if (base + kStepBytes >= prm.size) {
           done = true;
         }
+        ExpandMask(KeepMask(first_byte, begin, end), keep);
       }
-      const uint32_t keep = KeepMask(first_byte, begin, end);
 
-      /* token starts in this lane's 16 bytes */
-      uint32_t starts, row_starts = 0;
+      /* token starts in this lane's 16 bytes, as flags */
+      uint32_t starts[4], row_starts[4];
       if (FMT == kCSV) {
         /* a field starts after a comma or at a line start, unless that byte is an EOL
-           (csv_parser.h:79-95: a trailing comma yields no extra column).  The raw masks are
+           (csv_parser.h:79-95: a trailing comma yields no extra column).  Unmasked flags are
            used for "what precedes me" so that the line start at `begin` is seen. */
-        uint32_t up_c = __shfl_up_sync(0xffffffffu, raw.a >> 15, 1);
-        uint32_t up_e = __shfl_up_sync(0xffffffffu, raw.eol >> 15, 1);
+        uint32_t up_a = __shfl_up_sync(0xffffffffu, fa[3], 1);
+        uint32_t up_e = __shfl_up_sync(0xffffffffu, fe[3], 1);
         if (lane == 0) {
-          up_c = prev_a;
-          up_e = prev_eol;
+          up_a = carry_a;
+          up_e = carry_e;
         }
-        const uint32_t after_comma = ((raw.a << 1) | up_c) & 0xffffu;
-        const uint32_t after_eol = ((raw.eol << 1) | up_e) & 0xffffu;
-        row_starts = after_eol & ~raw.eol & keep;
-        starts = (after_comma | after_eol) & ~raw.eol & keep;
-        prev_a = __shfl_sync(0xffffffffu, raw.a >> 15, 31);
-        prev_eol = __shfl_sync(0xffffffffu, raw.eol >> 15, 31);
+        carry_a = __shfl_sync(0xffffffffu, fa[3], 31);
+        carry_e = __shfl_sync(0xffffffffu, fe[3], 31);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t after_sep = __funnelshift_l(i == 0 ? up_a : fa[i - 1], fa[i], 8);
+          const uint32_t after_eol = __funnelshift_l(i == 0 ? up_e : fe[i - 1], fe[i], 8);
+          starts[i] = after_sep & ~fe[i] & 0x80808080u;
+          row_starts[i] = after_eol & ~fe[i] & 0x80808080u;
+          if (!interior) {
+            starts[i] &= keep[i];
+            row_starts[i] &= keep[i];
+          }
+        }
       } else {
         /* a digit run cannot cross `begin` or `end` (both follow an EOL byte) */
-        const uint32_t runs = raw.a & keep;
-        uint32_t up_a = __shfl_up_sync(0xffffffffu, runs >> 15, 1);
-        if (lane == 0) up_a = prev_a;
-        starts = runs & ~((runs << 1) | up_a);
-        prev_a = __shfl_sync(0xffffffffu, runs >> 15, 31);
+        if (!interior) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) fa[i] &= keep[i];
+        }
+        uint32_t up_a = __shfl_up_sync(0xffffffffu, fa[3], 1);
+        if (lane == 0) up_a = carry_a;
+        carry_a = __shfl_sync(0xffffffffu, fa[3], 31);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          starts[i] = fa[i] & ~__funnelshift_l(i == 0 ? up_a : fa[i - 1], fa[i], 8);
+          row_starts[i] = 0u;
+        }
+      }
+      /* flags sit at bit 7 of each byte: four words interleave into one for a single popc */
+      const uint32_t mine =
+          __popc(starts[0] | (starts[1] >> 1) | (starts[2] >> 2) | (starts[3] >> 3));
+      if constexpr (FMT == kCSV && !EMIT) {
+        /* counting a CSV chunk needs no per-field work when the label is absent or is column 0
+           (every row then owns exactly one label field): rows and fields are popcounts */
+        if (prm.label_column <= 0) {
+          csv_fields += mine;
+          csv_rows += __popc(row_starts[0] | (row_starts[1] >> 1) | (row_starts[2] >> 2) |
+                             (row_starts[3] >> 3));
+          continue;
+        }
       }
       /* compact them, in file order, behind the tokens left from the previous step */
       {
-        const uint32_t mine = __popc(starts);
         const uint32_t incl = WarpInclusiveSum(mine, lane);
         uint32_t slot = fill + incl - mine;
-        uint32_t bits = starts;
-        while (bits != 0u) {
-          const uint32_t b = __ffs(bits) - 1;
-          bits &= bits - 1u;
-          uint32_t entry = first_byte + b;
-          if (FMT == kCSV) entry |= ((row_starts >> b) & 1u) << 31;
-          ws.tokens[slot++] = entry;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint32_t bits = starts[i];
+          while (bits != 0u) {
+            const uint32_t b = __ffs(bits) - 1;   /* 8 * byte + 7 */
+            bits &= bits - 1u;
+            uint32_t entry = first_byte + 4u * i + (b >> 3);
+            if (FMT == kCSV) entry |= ((row_starts[i] >> b) & 1u) << 31;
+            ws.tokens[slot++] = entry;
+          }
         }
         fill += __shfl_sync(0xffffffffu, incl, 31);
         __syncwarp();
@@ -655,6 +727,15 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
       }
     }
     if constexpr (EMIT && FMT != kCSV) DrainRoleQueues<FMT, IdxT>(prm, txt, ws, st, lane, true);
+    if constexpr (FMT == kCSV && !EMIT) {
+      if (prm.label_column <= 0) {
+        const uint32_t rows = __reduce_add_sync(0xffffffffu, csv_rows);
+        const uint32_t fields = __reduce_add_sync(0xffffffffu, csv_fields);
+        st.seen[kRows] = rows;
+        st.seen[kNnz] = fields - (prm.label_column == 0 ? rows : 0u);
+        st.seen[kValues] = st.seen[kNnz];
+      }
+    }
   }
 
   if (EMIT) {

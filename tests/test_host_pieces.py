@@ -43,6 +43,68 @@ def test_device_token_code_matches_oracle(emul, oracle):
         assert emul.emul_atoll(t.encode()) == oracle.atoll(t), t
 
 
+def test_window_fast_paths_match_oracle(emul, oracle):
+    """ToFloatFast / ToUintFast (register-window fast paths with fallback) against the oracle, with
+    the token at every alignment, followed by each kind of terminator, near the end of the chunk."""
+    emul.emul_fast_strtof_bits.restype = C.c_uint32
+    emul.emul_fast_strtof_bits.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_int)]
+    emul.emul_fast_strtouint.restype = C.c_uint64
+    emul.emul_fast_strtouint.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_int,
+                                         C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    rnd = random.Random(77)
+    terms = [",", " ", "\n", ":", "\t", "\r\n", "x", ",,", " 5", ":7", ""]
+    fast_f = fast_u = total = 0
+    toks = ["-7.60915", "0.137604", "7", "-", "+", ".", "-.5", "5.", "1234567.1234567", "12345678.5",
+            "0.12345678", "16777217", "1e5", "2.5e-3", "9999999.9999999", "-0", "007.500", " 5", "\t1",
+            "0.0000001", "1.", "+1.5", "--5", "1.2.3", "0.", "-1234567.1234567", "+1234567.1234567"]
+    for _ in range(60000):
+        k = rnd.random()
+        if k < 0.4:
+            toks.append("%.6g" % rnd.uniform(-10, 10))
+        elif k < 0.6:
+            toks.append("%.7g" % rnd.uniform(0, 1e6))
+        elif k < 0.8:
+            toks.append("".join(rnd.choice("0123456789") for _ in range(rnd.randint(1, 9))) +
+                        rnd.choice(["", ".", "." + "".join(rnd.choice("0123456789") for _ in range(rnd.randint(0, 9)))]))
+        else:
+            toks.append("".join(rnd.choice("0123456789" * 3 + "+-.eE") for _ in range(rnd.randint(1, 20))))
+    for tok in toks:
+        lead = "," * rnd.randint(0, 9)
+        tail = rnd.choice(terms) + ("123.5,\n" * rnd.randint(0, 4))
+        buf = (lead + tok + tail).encode()
+        took = C.c_int()
+        got = emul.emul_fast_strtof_bits(buf, len(buf), len(lead), C.byref(took))
+        want, _ = oracle.strtof_bits((tok + tail).encode())
+        assert got == want, (tok, tail, lead)
+        fast_f += took.value
+        total += 1
+    # on the bench's token shape (%.6g, other text following) the window path is THE path
+    fast_typ = 0
+    for i in range(5000):
+        tok = "%.6g" % rnd.uniform(-10, 10)
+        buf = ("," * (i % 16) + tok + ",-3.25,7.5,0.001,1,2,3\n").encode()
+        took = C.c_int()
+        emul.emul_fast_strtof_bits(buf, len(buf), i % 16, C.byref(took))
+        fast_typ += took.value
+    assert fast_typ >= 4950, fast_typ
+    n_u = 0
+    for _ in range(60000):
+        tok = "".join(rnd.choice("0123456789") for _ in range(rnd.randint(0, 21)))
+        if rnd.random() < 0.1:
+            tok = rnd.choice(["+", "-", " ", "."]) + tok
+        lead = " " * rnd.randint(0, 9)
+        tail = rnd.choice([":", " ", "\n", ":0.5 ", ".5", "e", ""]) + ("9:1 " * rnd.randint(0, 6))
+        buf = (lead + tok + tail).encode()
+        for w in (4, 8):
+            th, took = C.c_int(), C.c_int()
+            v = emul.emul_fast_strtouint(buf, len(buf), len(lead), w, C.byref(th), C.byref(took))
+            ov, othrew = oracle.strtouint((tok + tail).encode(), w)
+            assert bool(th.value) == othrew and (othrew or v == ov), (tok, tail, w)
+            fast_u += took.value
+            n_u += 1
+    assert fast_u > n_u // 4
+
+
 def test_digitchar_class(emul):
     want = set(b"0123456789+-.eE")
     for c in range(256):
