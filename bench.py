@@ -49,6 +49,20 @@ def parse_args():
     return ap.parse_args()
 
 
+def ncu_traffic(kernel_substr):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the
+    committed `ncu --set full` capture of this same workload (profiles/current_ncu.metrics.json,
+    written by profiles/summarize_ncu.py). bench.py itself never runs under a profiler."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "current_ncu.metrics.json")) as f:
+            for k in json.load(f):
+                if kernel_substr in k.get("kernel", ""):
+                    return float(k["dram_bytes_per_launch"])
+    except Exception:
+        pass
+    return None
+
+
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -301,7 +315,8 @@ def main():
     achieved = b_alg / (emit_ms * 1e-3) / GB
     path_achieved = b_alg / ((emit_ms + count_ms + scan_ms) * 1e-3) / GB
     roofline = {"bound": "hbm", "kernel": "WalkText<CSV,uint32,EMIT>", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic("WalkText<2, unsigned int, 1>"),
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": b_alg,
                 "launch_ms": emit_ms,
                 "all_kernels": {"count_ms": count_ms, "scan_ms": scan_ms, "emit_ms": emit_ms,
