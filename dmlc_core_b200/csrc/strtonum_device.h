@@ -252,11 +252,9 @@ B200P_HD uint64_t ToQid(const Text &t, uint32_t p) {
  * IEEE fp64 division.
  * ------------------------------------------------------------------------------------------ */
 #if defined(__CUDA_ARCH__)
-B200P_D void Load8(const uint8_t *p, uint32_t *lo, uint32_t *hi) {
-  const uint2 v = __ldg(reinterpret_cast<const uint2 *>(p));
-  *lo = v.x;
-  *hi = v.y;
-}
+B200P_D uint32_t Load4(const uint8_t *p) { return __ldg(reinterpret_cast<const uint32_t *>(p)); }
+/* x << s for s = 0..32 (32 gives 0) */
+B200P_D uint32_t ShlClamp(uint32_t x, uint32_t s) { return __funnelshift_lc(0u, x, s); }
 /* bytes k.. of the 8-byte pair (hi:lo), k = 0..3 */
 B200P_D uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) { return __funnelshift_r(lo, hi, k * 8u); }
 B200P_D int FirstSet(uint32_t x) { return __ffs(static_cast<int>(x)) - 1; }
@@ -265,15 +263,12 @@ B200P_D float Fraction8(uint32_t f8) {
   return __double2float_rn(__dmul_rn(__uint2double_rn(f8), 1e-8));
 }
 #else
-inline void Load8(const uint8_t *p, uint32_t *lo, uint32_t *hi) {
-  uint32_t a = 0, b = 0;
-  for (int i = 0; i < 4; ++i) {
-    a |= static_cast<uint32_t>(p[i]) << (8 * i);
-    b |= static_cast<uint32_t>(p[i + 4]) << (8 * i);
-  }
-  *lo = a;
-  *hi = b;
+inline uint32_t Load4(const uint8_t *p) {
+  uint32_t a = 0;
+  for (int i = 0; i < 4; ++i) a |= static_cast<uint32_t>(p[i]) << (8 * i);
+  return a;
 }
+inline uint32_t ShlClamp(uint32_t x, uint32_t s) { return s >= 32u ? 0u : (x << s); }
 inline uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) {
   return k == 0u ? lo : ((lo >> (8u * k)) | (hi << (32u - 8u * k)));
 }
@@ -291,17 +286,12 @@ struct Window {
 };
 
 /* false if the aligned loads would touch memory past the chunk
-   ([p & ~7, (p & ~7) + 24) must be readable) */
+   ([p & ~3, (p & ~3) + 20) must be readable) */
 B200P_HD bool LoadWindow(const Text &t, uint32_t p, Window *w) {
-  const uint32_t a = p & ~7u;
-  if (a + 24u > t.size) return false;
-  uint32_t w0, w1, w2, w3, w4, w5;
-  Load8(t.data + a, &w0, &w1);
-  Load8(t.data + a + 8, &w2, &w3);
-  Load8(t.data + a + 16, &w4, &w5);
-  if ((p & 4u) != 0u) {
-    w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5;
-  }
+  const uint32_t a = p & ~3u;
+  if (a + 20u > t.size) return false;
+  const uint32_t w0 = Load4(t.data + a), w1 = Load4(t.data + a + 4), w2 = Load4(t.data + a + 8),
+                 w3 = Load4(t.data + a + 12), w4 = Load4(t.data + a + 16);
   const uint32_t k = p & 3u;
   w->x0 = BytesFrom(w0, w1, k);
   w->x1 = BytesFrom(w1, w2, k);
@@ -342,24 +332,29 @@ B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
     used = 1;
   }
   /* integer digits: at most 7, so that the reference's fp32 accumulation is exact (< 2^24) */
-  const uint32_t nd0 = NonDigitFlags(w.x0), nd1 = NonDigitFlags(w.x1);
-  uint32_t n1;
+  const uint32_t nd0 = NonDigitFlags(w.x0);
+  uint32_t n1, term, ip;
   if (nd0 != 0u) {
-    n1 = static_cast<uint32_t>(FirstSet(nd0)) >> 3;
-  } else if (nd1 != 0u) {
-    n1 = 4u + (static_cast<uint32_t>(FirstSet(nd1)) >> 3);
+    /* 0..3 digits, all in the first word: left-pad them to four places and pack */
+    const uint32_t bit = static_cast<uint32_t>(FirstSet(nd0)) & ~7u;   /* 8 * n1 */
+    n1 = bit >> 3;
+    term = (w.x0 >> bit) & 0xffu;
+    ip = Pack4(ShlClamp(w.x0 & 0x0f0f0f0fu, 32u - bit));
   } else {
-    return false;
-  }
-  uint32_t term = ByteOf(w.x0, w.x1, n1);
-  const uint32_t y0 = w.x0 & 0x0f0f0f0fu, y1 = w.x1 & 0x0f0f0f0fu;
-  uint32_t ip = 0;
+    const uint32_t nd1 = NonDigitFlags(w.x1);
+    if (nd1 == 0u) return false;            /* >= 8 integer digits */
+    const uint32_t bit = static_cast<uint32_t>(FirstSet(nd1)) & ~7u;
+    n1 = 4u + (bit >> 3);
+    term = (w.x1 >> bit) & 0xffu;
+    /* 4..7 digits: the first four packed, the rest appended one by one */
+    ip = Pack4(w.x0 & 0x0f0f0f0fu);
+    const uint32_t y1 = w.x1 & 0x0f0f0f0fu;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (uint32_t i = 0; i < 7u; ++i) {
-    const uint32_t d = ((i < 4u ? y0 : y1) >> ((i & 3u) * 8u)) & 0xffu;
-    if (i < n1) ip = ip * 10u + d;
+    for (uint32_t i = 0; i < 3u; ++i) {
+      if (4u + i < n1) ip = ip * 10u + ((y1 >> (8u * i)) & 0xffu);
+    }
   }
   float v = U32ToFloat(ip);
   used += n1;
@@ -377,25 +372,23 @@ B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
       a = w.x2; b = w.x3; c = 0u;
     }
     const uint32_t r0 = BytesFrom(a, b, f0 & 3u), r1 = BytesFrom(b, c, f0 & 3u);
-    const uint32_t ndr0 = NonDigitFlags(r0), ndr1 = NonDigitFlags(r1);
-    uint32_t n2, m0, m1;
+    const uint32_t ndr0 = NonDigitFlags(r0);
+    uint32_t n2, f8;
     if (ndr0 != 0u) {
       const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr0)) & ~7u;
       n2 = bit >> 3;
-      m0 = (1u << bit) - 1u;
-      m1 = 0u;
-    } else if (ndr1 != 0u) {
+      term = (r0 >> bit) & 0xffu;
+      f8 = Pack4(r0 & 0x0f0f0f0fu & ((1u << bit) - 1u)) * 10000u;
+    } else {
+      const uint32_t ndr1 = NonDigitFlags(r1);
+      if (ndr1 == 0u) return false;          /* >= 8 fraction digits */
       const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr1)) & ~7u;
       n2 = 4u + (bit >> 3);
-      m0 = 0xffffffffu;
-      m1 = (1u << bit) - 1u;
-    } else {
-      return false;                          /* >= 8 fraction digits */
+      term = (r1 >> bit) & 0xffu;
+      f8 = Pack4(r0 & 0x0f0f0f0fu) * 10000u + Pack4(r1 & 0x0f0f0f0fu & ((1u << bit) - 1u));
     }
     used += 1u + n2;
     if (used > 15u) return false;            /* the terminator must be a real byte of the window */
-    term = ByteOf(r0, r1, n2);
-    const uint32_t f8 = Pack4(r0 & 0x0f0f0f0fu & m0) * 10000u + Pack4(r1 & 0x0f0f0f0fu & m1);
     v = AddRn(v, Fraction8(f8));
   }
   if ((term | 0x20u) == 'e') return false;   /* exponent: general code */

@@ -69,6 +69,9 @@ struct WalkParams {
   uint32_t range_bytes;    /* multiple of kStepBytes */
   uint32_t num_ranges;
   int32_t label_column;    /* CSV */
+  uint32_t four;           /* always 4. Passed in so that the compiler cannot fold `acc * 4 + e`
+                              into a shift-add on the (saturated) ALU pipe: as a run-time value
+                              it stays an IMAD on the otherwise idle FMA pipe. */
   uint32_t *counts;        /* [kNumCounters][num_ranges]: pass 1 writes counts, the scan rewrites
                               them in place as exclusive prefixes within tiles of kScanTile */
   uint32_t *tile_base;     /* [kNumCounters][num_tiles]: exclusive prefix of the tile totals */
@@ -136,32 +139,42 @@ __device__ __forceinline__ Masks16 Classify(const uint4 v) {
   return m;
 }
 
-/* Class flags of 16 bytes, one word at a time, bit 7 of each byte (no bit gathering):
-   fa = digit-run bytes (LibSVM/LibFM) or separators ',' | EOL (CSV); fe = EOL bytes. */
+/*
+ * Byte classes through a 256-byte table in shared memory.  The SWAR classifier costs ~50 logic
+ * instructions per 16 bytes, all on the half-rate ALU pipe that bounds these kernels; the table
+ * walk costs one PRMT (ALU), one LDS.U8 (LSU) and one IMAD (FMA pipe) per byte.  ASCII bytes map
+ * to distinct banks or to the same word (broadcast), so the lookups are conflict-free.
+ *
+ * Table entry: bit 0 = class A (LibSVM/LibFM: digit-run byte; CSV: ',' or EOL), bit 1 = EOL.
+ * Result: a 32-bit interleaved mask, bit 2j = A of byte j, bit 2j+1 = EOL of byte j.
+ */
+constexpr uint32_t kEven = 0x55555555u;
+
 template <int FMT>
-__device__ __forceinline__ void ClassifyFlags(const uint4 v, uint32_t (&fa)[4], uint32_t (&fe)[4]) {
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const uint32_t xm = w[i] & 0x7f7f7f7fu;
-    const uint32_t not_lf = (xm ^ 0x0a0a0a0au) + 0x7f7f7f7fu;   /* bit 7 clear iff '\n' */
-    const uint32_t not_cr = (xm ^ 0x0d0d0d0du) + 0x7f7f7f7fu;
-    fe[i] = ~(not_lf & not_cr) & ~w[i] & 0x80808080u;
-    if (FMT == kCSV) {
-      const uint32_t not_comma = (xm ^ 0x2c2c2c2cu) + 0x7f7f7f7fu;
-      fa[i] = ~(not_lf & not_cr & not_comma) & ~w[i] & 0x80808080u;
-    } else {
-      fa[i] = WordDigitChar(w[i]) & 0x80808080u;
-    }
-  }
+__device__ __forceinline__ uint32_t ClassEntry(uint32_t byte) {
+  const bool eol = byte == '\n' || byte == '\r';
+  const bool a = FMT == kCSV ? (eol || byte == ',') : IsDigitChar(byte);
+  return (a ? 1u : 0u) | (eol ? 2u : 0u);
 }
 
-/* 16-bit byte mask -> four words with bit 7 of each selected byte set */
-__device__ __forceinline__ void ExpandMask(uint32_t mask16, uint32_t (&out)[4]) {
+__device__ __forceinline__ uint32_t ClassifyLut(const uint4 v, const uint8_t *lut, uint32_t four) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  uint32_t lo = 0, hi = 0; /* two Horner chains: bytes 7..0 and 15..8 */
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    out[i] = ((((mask16 >> (4 * i)) & 0xfu) * 0x00204081u) & 0x01010101u) << 7;
+  for (int j = 7; j >= 0; --j) {
+    lo = lo * four + lut[__byte_perm(w[j >> 2], 0u, 0x4440u | (j & 3))];
+    hi = hi * four + lut[__byte_perm(w[2 + (j >> 2)], 0u, 0x4440u | (j & 3))];
   }
+  return lo | (hi << 16);
+}
+
+/* 16-bit byte mask -> the even bits of a 32-bit interleaved mask */
+__device__ __forceinline__ uint32_t Spread16(uint32_t m) {
+  m = (m | (m << 8)) & 0x00ff00ffu;
+  m = (m | (m << 4)) & 0x0f0f0f0fu;
+  m = (m | (m << 2)) & 0x33333333u;
+  m = (m | (m << 1)) & 0x55555555u;
+  return m;
 }
 
 /* 16 bytes at `pos` (multiple of 16); bytes at or past `size` read as NUL */
@@ -335,7 +348,7 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
                                            WarpScratch<FMT> &ws, WalkState &st, uint32_t head,
                                            uint32_t count, int lane) {
   const bool active = lane < count;
-  const uint32_t at = active ? ws.tokens[head + lane] : 0u;
+  const uint32_t at = active ? (ws.tokens[head + lane] >> 1) : 0u;
 
   /* ---- look back over the separator in front of this token ---- */
   bool line_start = true;   /* separator contains an EOL (or the chunk starts here) */
@@ -486,7 +499,7 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
 
 /*
  * One group of <= 32 CSV fields, one per lane (reference csv_parser.h:73-102).  A queue entry
- * is the byte position of the field start with bit 31 set when the field opens a row.
+ * is twice the byte position of the field start, plus one when the field opens a row.
  * Every field is converted with ToFloat; column == label_column goes to label[], every other
  * column to (index = running column id without the label column, value).
  */
@@ -496,8 +509,8 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
                                            uint32_t count, int lane) {
   const bool active = lane < count;
   const uint32_t entry = active ? ws.tokens[head + lane] : 0u;
-  const bool row_start = active && (entry >> 31) != 0u;
-  const uint32_t at = entry & 0x7fffffffu;
+  const bool row_start = active && (entry & 1u) != 0u;
+  const uint32_t at = entry >> 1;
   const uint32_t rs_m = __ballot_sync(0xffffffffu, row_start);
   const uint32_t below = rs_m & LaneMaskLe();
   uint32_t col;
@@ -542,6 +555,10 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
 template <int FMT, typename IdxT, bool EMIT>
 __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   __shared__ WarpScratch<FMT> scratch[kWarpsPerCta];
+  __shared__ __align__(16) uint8_t lut[256];
+  static_assert(kCtaThreads == 256, "one thread fills one entry of the class table");
+  lut[threadIdx.x] = static_cast<uint8_t>(ClassEntry<FMT>(threadIdx.x));
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const uint32_t range = blockIdx.x * kWarpsPerCta + warp;
@@ -595,111 +612,77 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   if (begin < hi) {
     uint32_t fill = 0;          /* tokens waiting in ws.tokens */
     uint32_t end = prm.size;    /* tightened once the closing EOL is seen */
-    /* class flags of the last 4 bytes of the previous step (only the top byte's flag is used):
-       LibSVM/LibFM: byte was part of a digit run; CSV: byte was a comma or an EOL */
-    uint32_t carry_a = FMT == kCSV ? 0x80000000u : 0u; /* the EOL before `begin` is a separator */
-    uint32_t carry_e = 0x80000000u; /* CSV: an EOL precedes `begin` (a line starts there) */
+    /* class bits (A | EOL << 1) of the byte before this step's first byte.
+       CSV: the EOL before `begin` is a separator and an EOL; LibSVM/LibFM: it is no digit */
+    uint32_t carry = FMT == kCSV ? 3u : 0u;
     bool done = false;
     uint32_t csv_fields = 0, csv_rows = 0; /* per-lane tallies of the CSV counting shortcut */
     for (uint32_t base = begin & ~uint32_t(kStepBytes - 1); !done; base += kStepBytes) {
       const uint32_t first_byte = base + 16u * lane;
       /* interior step: wholly owned, wholly inside the chunk, and too early to hold the EOL
-         that closes the region -- no masks, no bounds checks (the common case: 14 of 16 steps
-         of an 8 KiB range) */
+         that closes the region -- no masks, no bounds checks (14 of 16 steps of an 8 KiB range) */
       const bool interior = base >= begin && base + kStepBytes <= hi - 1u;
-      uint32_t fa[4], fe[4];    /* per-word class flags, bit 7 of each byte */
-      uint32_t keep[4];
+      uint32_t cls;             /* interleaved class mask of my 16 bytes */
+      uint32_t keep = kEven;    /* owned bytes, on the even bits */
       if (interior) {
-        ClassifyFlags<FMT>(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), fa, fe);
+        cls = ClassifyLut(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), lut, prm.four);
       } else {
-        ClassifyFlags<FMT>(Load16(prm.text, prm.size, first_byte), fa, fe);
+        cls = ClassifyLut(Load16(prm.text, prm.size, first_byte), lut, prm.four);
         /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
-        uint32_t closing[4];
-        ExpandMask(KeepMask(first_byte, hi - 1u, prm.size), closing);
-        uint32_t mine = 0xffffffffu; /* byte offset of my first closing EOL */
-#pragma unroll
-        for (int i = 3; i >= 0; --i) {
-          const uint32_t c = fe[i] & closing[i];
-          if (c != 0u) mine = 4u * i + ((__ffs(c) - 1) >> 3);
-        }
-        const uint32_t who = __ballot_sync(0xffffffffu, mine != 0xffffffffu);
+        const uint32_t closing = (cls >> 1) & Spread16(KeepMask(first_byte, hi - 1u, prm.size));
+        const uint32_t who = __ballot_sync(0xffffffffu, closing != 0u);
         if (who != 0u) {
           const int src = __ffs(who) - 1;
-          end = base + 16u * src + __shfl_sync(0xffffffffu, mine, src) + 1u;
+          const uint32_t cs = __shfl_sync(0xffffffffu, closing, src);
+          end = base + 16u * src + ((__ffs(cs) - 1) >> 1) + 1u;
           done = true;
         } else if (base + kStepBytes >= prm.size) {
           done = true;
         }
-        ExpandMask(KeepMask(first_byte, begin, end), keep);
+        keep = Spread16(KeepMask(first_byte, begin, end));
       }
 
-      /* token starts in this lane's 16 bytes, as flags */
-      uint32_t starts[4], row_starts[4];
+      /* token starts in this lane's 16 bytes (even bits), CSV row starts likewise */
+      uint32_t up = __shfl_up_sync(0xffffffffu, cls >> 30, 1);
+      if (lane == 0) up = carry;
+      carry = __shfl_sync(0xffffffffu, cls >> 30, 31);
+      uint32_t starts, row_starts = 0;
       if (FMT == kCSV) {
         /* a field starts after a comma or at a line start, unless that byte is an EOL
-           (csv_parser.h:79-95: a trailing comma yields no extra column).  Unmasked flags are
+           (csv_parser.h:79-95: a trailing comma yields no extra column).  Unmasked classes are
            used for "what precedes me" so that the line start at `begin` is seen. */
-        uint32_t up_a = __shfl_up_sync(0xffffffffu, fa[3], 1);
-        uint32_t up_e = __shfl_up_sync(0xffffffffu, fe[3], 1);
-        if (lane == 0) {
-          up_a = carry_a;
-          up_e = carry_e;
-        }
-        carry_a = __shfl_sync(0xffffffffu, fa[3], 31);
-        carry_e = __shfl_sync(0xffffffffu, fe[3], 31);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint32_t after_sep = __funnelshift_l(i == 0 ? up_a : fa[i - 1], fa[i], 8);
-          const uint32_t after_eol = __funnelshift_l(i == 0 ? up_e : fe[i - 1], fe[i], 8);
-          starts[i] = after_sep & ~fe[i] & 0x80808080u;
-          row_starts[i] = after_eol & ~fe[i] & 0x80808080u;
-          if (!interior) {
-            starts[i] &= keep[i];
-            row_starts[i] &= keep[i];
-          }
-        }
+        const uint32_t before = (cls << 2) | up;        /* classes of the previous byte */
+        const uint32_t not_eol = ~(cls >> 1) & keep;
+        starts = before & not_eol;
+        row_starts = (before >> 1) & not_eol;
       } else {
         /* a digit run cannot cross `begin` or `end` (both follow an EOL byte) */
-        if (!interior) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) fa[i] &= keep[i];
-        }
-        uint32_t up_a = __shfl_up_sync(0xffffffffu, fa[3], 1);
-        if (lane == 0) up_a = carry_a;
-        carry_a = __shfl_sync(0xffffffffu, fa[3], 31);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          starts[i] = fa[i] & ~__funnelshift_l(i == 0 ? up_a : fa[i - 1], fa[i], 8);
-          row_starts[i] = 0u;
-        }
+        const uint32_t runs = cls & keep;
+        starts = runs & ~((runs << 2) | (up & 1u));
       }
-      /* flags sit at bit 7 of each byte: four words interleave into one for a single popc */
-      const uint32_t mine =
-          __popc(starts[0] | (starts[1] >> 1) | (starts[2] >> 2) | (starts[3] >> 3));
+      const uint32_t mine = __popc(starts);
       if constexpr (FMT == kCSV && !EMIT) {
         /* counting a CSV chunk needs no per-field work when the label is absent or is column 0
            (every row then owns exactly one label field): rows and fields are popcounts */
         if (prm.label_column <= 0) {
           csv_fields += mine;
-          csv_rows += __popc(row_starts[0] | (row_starts[1] >> 1) | (row_starts[2] >> 2) |
-                             (row_starts[3] >> 3));
+          csv_rows += __popc(row_starts);
           continue;
         }
       }
-      /* compact them, in file order, behind the tokens left from the previous step */
+      /* compact them, in file order, behind the tokens left from the previous step.
+         Queue entry = 2 * byte position (+ 1 for a CSV field that opens a row). */
       {
         const uint32_t incl = WarpInclusiveSum(mine, lane);
         uint32_t slot = fill + incl - mine;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          uint32_t bits = starts[i];
-          while (bits != 0u) {
-            const uint32_t b = __ffs(bits) - 1;   /* 8 * byte + 7 */
-            bits &= bits - 1u;
-            uint32_t entry = first_byte + 4u * i + (b >> 3);
-            if (FMT == kCSV) entry |= ((row_starts[i] >> b) & 1u) << 31;
-            ws.tokens[slot++] = entry;
-          }
+        uint32_t bits = starts;
+        const uint32_t first2 = 2u * first_byte;
+        while (bits != 0u) {
+          const uint32_t b = __ffs(bits) - 1;     /* 2 * byte offset */
+          bits &= bits - 1u;
+          uint32_t entry = first2 + b;
+          if (FMT == kCSV) entry += (row_starts >> b) & 1u;
+          ws.tokens[slot++] = entry;
         }
         fill += __shfl_sync(0xffffffffu, incl, 31);
         __syncwarp();
