@@ -322,6 +322,33 @@ def main():
                 "all_kernels": {"count_ms": count_ms, "scan_ms": scan_ms, "emit_ms": emit_ms,
                                 "achieved": path_achieved, "frac": path_achieved / peak}}
 
+    # ---------------- the link the end-to-end number rides on -------------------------------------
+    link = None
+    if not args.no_e2e:
+        nb = min(n, 512 << 20)
+        d_tmp = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        h_out = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+
+        def copies(up, down, reps=4):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                if up:
+                    with torch.cuda.stream(s_up):
+                        d_tmp.copy_(host[:nb], non_blocking=True)
+                if down:
+                    with torch.cuda.stream(s_dn):
+                        h_out.copy_(dev[:nb], non_blocking=True)
+            torch.cuda.synchronize()
+            return reps * nb / (time.perf_counter() - t0) / GB
+
+        copies(True, True, 1)
+        link = {"h2d_only_GBps": copies(True, False), "d2h_only_GBps": copies(False, True),
+                "h2d_with_concurrent_d2h_GBps": copies(True, True),
+                "how": "pinned cudaMemcpyAsync of %d MiB blocks, 4 reps" % (nb >> 20)}
+        del d_tmp, h_out
+
     # ---------------- end to end: pinned host text -> pinned host CSR -------------------------
     e2e = None
     if not args.no_e2e:
@@ -359,7 +386,9 @@ def main():
         e2e = {"value": world * text_bytes / e2e_s / GB, "unit": "GB/s",
                "h2d_bytes_per_step": text_bytes, "d2h_bytes_per_step": d2h[0] // e2e_steps,
                "ms_per_step": e2e_s * 1e3, "chunk_bytes": args.chunk_mb << 20, "depth": 3,
-               "api": "b200p_submit / b200p_next (pinned host text in, pinned host CSR out)"}
+               "api": "b200p_submit / b200p_next (pinned host text in, pinned host CSR out)",
+               "link": link,
+               "frac_of_h2d_link_under_duplex": (text_bytes / e2e_s / GB) / link["h2d_with_concurrent_d2h_GBps"]}
         pe.close()
 
     # ---------------- CPU baseline (rank 0, N == 1) -------------------------------------------

@@ -226,13 +226,23 @@ static void LaunchWalk(const b200p_handle h, const WalkParams &p, cudaStream_t s
   }
 }
 
+/* Bytes of text one warp owns. Large ranges amortise the two partial steps at the ends of a range
+   (measured on the 1 GB CSV window: 8 KiB 1.24 ms, 16 KiB 1.18 ms, 32 KiB 1.17 ms per emit launch),
+   small chunks need small ranges to fill 148 SMs x ~48 resident warps. */
+static uint32_t RangeBytesFor(const b200p_handle h, uint64_t nbytes) {
+  if (h->range_bytes != 0u) return h->range_bytes;
+  if (nbytes >= (128ull << 20)) return 16384u;
+  if (nbytes >= (32ull << 20)) return 8192u;
+  return 4096u;
+}
+
 static WalkParams MakeParams(const b200p_handle h, const Slot &s) {
   WalkParams p;
   std::memset(&p, 0, sizeof(p));
   p.text = s.text;
   p.size = static_cast<uint32_t>(s.nbytes);
-  p.range_bytes = h->range_bytes;
-  p.num_ranges = static_cast<uint32_t>((s.nbytes + h->range_bytes - 1) / h->range_bytes);
+  p.range_bytes = RangeBytesFor(h, s.nbytes);
+  p.num_ranges = static_cast<uint32_t>((s.nbytes + p.range_bytes - 1) / p.range_bytes);
   p.label_column = h->cfg.label_column;
   p.four = 4u;
   p.counts = s.d_counts;
@@ -274,7 +284,8 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
     std::memset(s->h_summary, 0, sizeof(ChunkSummary));
     return B200P_OK;
   }
-  const uint64_t ranges = (s->nbytes + h->range_bytes - 1) / h->range_bytes;
+  const uint32_t range_bytes = RangeBytesFor(h, s->nbytes);
+  const uint64_t ranges = (s->nbytes + range_bytes - 1) / range_bytes;
   if (ranges > s->counts_cap) {
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
     cudaFree(s->d_counts);
@@ -404,8 +415,9 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->cfg = *config;
   if (h->cfg.chunk_bytes == 0) h->cfg.chunk_bytes = 64ull << 20;
   if (h->cfg.chunk_bytes > B200P_MAX_CHUNK_BYTES) h->cfg.chunk_bytes = B200P_MAX_CHUNK_BYTES;
-  uint32_t rb = config->range_bytes > 0 ? static_cast<uint32_t>(config->range_bytes) : 8192u;
-  rb = std::max<uint32_t>(kStepBytes, (rb + kStepBytes - 1) / kStepBytes * kStepBytes);
+  /* 0 = choose per chunk (RangeBytesFor) */
+  uint32_t rb = config->range_bytes > 0 ? static_cast<uint32_t>(config->range_bytes) : 0u;
+  if (rb != 0u) rb = std::max<uint32_t>(kStepBytes, (rb + kStepBytes - 1) / kStepBytes * kStepBytes);
   h->range_bytes = rb;
   h->depth = config->depth > 0 ? std::min(config->depth, 8) : 3;
   h->lent_slot = -1;

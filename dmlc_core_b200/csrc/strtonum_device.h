@@ -311,10 +311,17 @@ B200P_HD uint32_t ByteOf(uint32_t lo, uint32_t hi, uint32_t i) {
   return ((i < 4u ? lo : hi) >> ((i & 3u) * 8u)) & 0xffu;
 }
 
-/* four digit values d0 d1 d2 d3 (one per byte, d0 in the low byte = most significant) -> number */
-B200P_HD uint32_t Pack4(uint32_t z) {
-  const uint32_t t = (z * 10u + (z >> 8)) & 0x00ff00ffu; /* d0d1 | d2d3 << 16 */
-  return (t & 0xffffu) * 100u + (t >> 16);
+/* four digit values d0 d1 d2 d3 (one per byte, d0 in the low byte = most significant) -> number,
+   added to `plus`.  z * 10 + (z >> 8) leaves d0d1 in byte 0 and d2d3 in byte 2 (bytes 1 and 3 are
+   by-products); a byte dot product with weights (100, 0, 1, 0) finishes the job in one
+   instruction. */
+B200P_HD uint32_t Pack4(uint32_t z, uint32_t plus) {
+  const uint32_t t = z * 10u + (z >> 8);
+#if defined(__CUDA_ARCH__)
+  return __dp4a(t, 0x00010064u, plus);
+#else
+  return (t & 0xffu) * 100u + ((t >> 16) & 0xffu) + plus;
+#endif
 }
 
 B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
@@ -323,47 +330,41 @@ B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
   const uint32_t c0 = w.x0 & 0xffu;
   if (c0 <= 0x20u) return false;           /* whitespace / control first: general code */
   const bool negative = c0 == '-';
-  uint32_t used = 0;                        /* window bytes consumed so far */
-  if (negative || c0 == '+') {
-    w.x0 = BytesFrom(w.x0, w.x1, 1u);
-    w.x1 = BytesFrom(w.x1, w.x2, 1u);
-    w.x2 = BytesFrom(w.x2, w.x3, 1u);
-    w.x3 >>= 8;
-    used = 1;
-  }
+  const uint32_t s0 = (negative || c0 == '+') ? 1u : 0u;   /* sign bytes */
   /* integer digits: at most 7, so that the reference's fp32 accumulation is exact (< 2^24) */
-  const uint32_t nd0 = NonDigitFlags(w.x0);
-  uint32_t n1, term, ip;
+  const uint32_t nd0 = NonDigitFlags(w.x0) & (s0 != 0u ? 0xffffff00u : 0xffffffffu);
+  uint32_t term, ip, f0; /* f0 = window offset of the byte after the terminator of the digits */
   if (nd0 != 0u) {
-    /* 0..3 digits, all in the first word: left-pad them to four places and pack */
-    const uint32_t bit = static_cast<uint32_t>(FirstSet(nd0)) & ~7u;   /* 8 * n1 */
-    n1 = bit >> 3;
+    /* sign + digits end inside the first word: drop the sign byte, left-pad the digits to four
+       places and pack */
+    const uint32_t bit = static_cast<uint32_t>(FirstSet(nd0)) & ~7u;   /* 8 * (s0 + n1) */
+    f0 = (bit >> 3) + 1u;
     term = (w.x0 >> bit) & 0xffu;
-    ip = Pack4(ShlClamp(w.x0 & 0x0f0f0f0fu, 32u - bit));
+    const uint32_t digits = w.x0 & (s0 != 0u ? 0x0f0f0f00u : 0x0f0f0f0fu);
+    ip = Pack4(ShlClamp(digits, 32u - bit), 0u);
   } else {
     const uint32_t nd1 = NonDigitFlags(w.x1);
-    if (nd1 == 0u) return false;            /* >= 8 integer digits */
+    if (nd1 == 0u) return false;            /* digits run past the second word */
     const uint32_t bit = static_cast<uint32_t>(FirstSet(nd1)) & ~7u;
-    n1 = 4u + (bit >> 3);
+    const uint32_t n = 4u + (bit >> 3);     /* s0 + n1 = 4..7 */
+    f0 = n + 1u;
     term = (w.x1 >> bit) & 0xffu;
-    /* 4..7 digits: the first four packed, the rest appended one by one */
-    ip = Pack4(w.x0 & 0x0f0f0f0fu);
+    /* the first word packed (sign byte as a leading zero), the rest appended one by one */
+    ip = Pack4(w.x0 & (s0 != 0u ? 0x0f0f0f00u : 0x0f0f0f0fu), 0u);
     const uint32_t y1 = w.x1 & 0x0f0f0f0fu;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (uint32_t i = 0; i < 3u; ++i) {
-      if (4u + i < n1) ip = ip * 10u + ((y1 >> (8u * i)) & 0xffu);
+      if (4u + i < n) ip = ip * 10u + ((y1 >> (8u * i)) & 0xffu);
     }
   }
   float v = U32ToFloat(ip);
-  used += n1;
   if (term == '.') {
     /* fraction: the 8 bytes after the dot, digits beyond the run zeroed = the digits right-padded
        to 8 places; float(double(F8) * 1e-8) == float(double(f) / double(10^k)) for every k <= 8
        (exhaustive CPU check) */
-    const uint32_t f0 = n1 + 1u;            /* 1 .. 8 */
-    uint32_t a, b, c;
+    uint32_t a, b, c;                        /* f0 = 1 .. 8 */
     if (f0 < 4u) {
       a = w.x0; b = w.x1; c = w.x2;
     } else if (f0 < 8u) {
@@ -371,24 +372,24 @@ B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
     } else {
       a = w.x2; b = w.x3; c = 0u;
     }
-    const uint32_t r0 = BytesFrom(a, b, f0 & 3u), r1 = BytesFrom(b, c, f0 & 3u);
+    const uint32_t r0 = BytesFrom(a, b, f0 & 3u);
     const uint32_t ndr0 = NonDigitFlags(r0);
     uint32_t n2, f8;
     if (ndr0 != 0u) {
       const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr0)) & ~7u;
       n2 = bit >> 3;
       term = (r0 >> bit) & 0xffu;
-      f8 = Pack4(r0 & 0x0f0f0f0fu & ((1u << bit) - 1u)) * 10000u;
+      f8 = Pack4(r0 & 0x0f0f0f0fu & ((1u << bit) - 1u), 0u) * 10000u;
     } else {
+      const uint32_t r1 = BytesFrom(b, c, f0 & 3u);
       const uint32_t ndr1 = NonDigitFlags(r1);
       if (ndr1 == 0u) return false;          /* >= 8 fraction digits */
       const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr1)) & ~7u;
       n2 = 4u + (bit >> 3);
       term = (r1 >> bit) & 0xffu;
-      f8 = Pack4(r0 & 0x0f0f0f0fu) * 10000u + Pack4(r1 & 0x0f0f0f0fu & ((1u << bit) - 1u));
+      f8 = Pack4(r1 & 0x0f0f0f0fu & ((1u << bit) - 1u), Pack4(r0 & 0x0f0f0f0fu, 0u) * 10000u);
     }
-    used += 1u + n2;
-    if (used > 15u) return false;            /* the terminator must be a real byte of the window */
+    if (f0 + n2 > 15u) return false;         /* the terminator must be a real byte of the window */
     v = AddRn(v, Fraction8(f8));
   }
   if ((term | 0x20u) == 'e') return false;   /* exponent: general code */
