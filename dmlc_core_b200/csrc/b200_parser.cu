@@ -531,7 +531,8 @@ static int FreeSlotIndex(b200p_handle h) {
   for (size_t i = 0; i < h->slots.size(); ++i) {
     if (!h->slots[i].busy && static_cast<int>(i) != h->returned_slot) return static_cast<int>(i);
   }
-  if (static_cast<int>(h->slots.size()) < h->depth + 1) {
+  /* depth in flight + one held by the caller + one being filled by its reader */
+  if (static_cast<int>(h->slots.size()) < h->depth + 2) {
     h->slots.push_back(Slot());
     return static_cast<int>(h->slots.size()) - 1;
   }

@@ -15,6 +15,8 @@
 #include <dmlc/timer.h>
 
 #include <algorithm>
+#include <chrono>
+#include <future>
 #include <cstdlib>
 #include <cstring>
 #include <limits>
@@ -50,6 +52,7 @@ static int EnvInt(const char *name, int fallback) {
  *   DMLC_B200_DEVICE    CUDA device ordinal (default 0)
  *   DMLC_B200_CHUNK_MB  chunk size in MiB (default 64; the reference uses 8, input_split_base.h:40)
  *   DMLC_B200_DEPTH     chunks in flight (default 3)
+ *   DMLC_B200_READ_THREADS  threads of one parallel pread (default: half the cores, at most 8)
  */
 template <typename IndexType>
 class B200TextParser : public Parser<IndexType> {
@@ -80,9 +83,17 @@ class B200TextParser : public Parser<IndexType> {
       LOG(FATAL) << "dmlc_core_b200: cannot create the GPU parser: " << why;
     }
     if (text_ == NULL) source_->HintChunkSize(chunk_bytes_);
+#if B200_HAVE_TEXT_SPLIT
+    if (text_ != NULL && EnvInt("DMLC_B200_READ_THREADS", 0) > 0) {
+      text_->SetReadThreads(EnvInt("DMLC_B200_READ_THREADS", 0));
+    }
+#endif
   }
 
   virtual ~B200TextParser() {
+#if B200_HAVE_TEXT_SPLIT
+    CancelRead();
+#endif
     b200p_destroy(handle_);
     delete source_;
   }
@@ -90,6 +101,9 @@ class B200TextParser : public Parser<IndexType> {
   virtual void BeforeFirst(void) {
     /* discard what is still in flight, then rewind the source (reference text_parser.h:40-42;
        like there, BytesRead keeps counting across passes) */
+#if B200_HAVE_TEXT_SPLIT
+    CancelRead();
+#endif
     b200p_rowblock dropped;
     while (b200p_pending(handle_) > 0) {
       if (b200p_next(handle_, &dropped) != B200P_OK) break;
@@ -127,25 +141,36 @@ class B200TextParser : public Parser<IndexType> {
     while ((!exhausted_ || !backlog_.empty()) && b200p_pending(handle_) < depth_) {
 #if B200_HAVE_TEXT_SPLIT
       if (text_ != NULL) {
-        void *pinned = NULL;
-        uint64_t cap = 0;
-        Check(b200p_input_buffer(handle_, &pinned, &cap));
-        size_t n = text_->ReadLines(pinned, static_cast<size_t>(cap));
+        /* Read-ahead: the next chunk is read (parallel pread, straight into the pinned staging
+           buffer of a free pipeline slot) by a background task while this thread waits for the
+           GPU in b200p_next and while the consumer works on the block it was handed. The task
+           only fills memory; every call into the C ABI stays on the consumer thread. */
+        if (!read_ahead_.valid() && !StartRead()) break;   /* no staging buffer free right now */
+        if (b200p_pending(handle_) > 0 &&
+            read_ahead_.wait_for(std::chrono::seconds(0)) != std::future_status::ready) {
+          break;                                     /* results are waiting: let the read run */
+        }
+        size_t n = read_ahead_.get();                /* rethrows a dmlc::Error of the reader */
+        void *pinned = read_buffer_;
         if (n == TextSplit::kLineTooLong) {
           /* a single line longer than the staging buffer: read it through a growing heap
              buffer; b200p_submit then enlarges the slot */
-          size_t big = static_cast<size_t>(cap);
+          size_t big = read_capacity_;
           do {
             big *= 2;
             CHECK(big <= B200P_MAX_CHUNK_BYTES) << "a single line exceeds " << B200P_MAX_CHUNK_BYTES << " bytes";
             spill_.resize(big);
             n = text_->ReadLines(spill_.data(), big);
           } while (n == TextSplit::kLineTooLong);
-          if (n == 0) { exhausted_ = true; break; }
-          Check(b200p_submit(handle_, spill_.data(), n));
-          continue;
+          pinned = spill_.data();
         }
-        if (n == 0) { exhausted_ = true; break; }
+        if (n == 0) {
+          /* end of the partition: an empty chunk hands the borrowed staging buffer back
+             (it comes out of b200p_next as a block without rows, which Next() skips) */
+          exhausted_ = true;
+          Check(b200p_submit(handle_, read_buffer_, 0));
+          break;
+        }
         Check(b200p_submit(handle_, pinned, n));
         continue;
       }
@@ -176,8 +201,34 @@ class B200TextParser : public Parser<IndexType> {
         }
       }
     }
+#if B200_HAVE_TEXT_SPLIT
+    /* pipeline full: still start reading the chunk after it */
+    if (text_ != NULL && !exhausted_ && !read_ahead_.valid()) StartRead();
+#endif
   }
 
+#if B200_HAVE_TEXT_SPLIT
+  bool StartRead() {
+    void *pinned = NULL;
+    uint64_t cap = 0;
+    const int rc = b200p_input_buffer(handle_, &pinned, &cap);
+    if (rc == B200P_E_AGAIN) return false;
+    Check(rc);
+    read_buffer_ = pinned;
+    read_capacity_ = static_cast<size_t>(cap);
+    TextSplit *split = text_;
+    read_ahead_ = std::async(std::launch::async, [split, pinned, cap]() {
+      return split->ReadLines(pinned, static_cast<size_t>(cap));
+    });
+    return true;
+  }
+  void CancelRead() {
+    if (read_ahead_.valid()) {
+      try { read_ahead_.get(); } catch (...) {}
+      b200p_submit(handle_, read_buffer_, 0);   /* returns the borrowed staging buffer */
+    }
+  }
+#endif
   void Check(int rc) {
     if (rc == B200P_OK) return;
     /* B200P_E_PARSE carries the reference's CHECK text; everything surfaces as dmlc::Error */
@@ -198,6 +249,11 @@ class B200TextParser : public Parser<IndexType> {
   bool exhausted_;
   std::vector<char> spill_;
   std::vector<std::string> backlog_;
+#if B200_HAVE_TEXT_SPLIT
+  std::future<size_t> read_ahead_;   /* bytes the background read produced */
+  void *read_buffer_;
+  size_t read_capacity_;
+#endif
 };
 
 /* ---- factories: same signatures and argument handling as reference src/data.cc:21-60 ---- */
