@@ -245,6 +245,7 @@ static WalkParams MakeParams(const b200p_handle h, const Slot &s) {
   p.num_ranges = static_cast<uint32_t>((s.nbytes + p.range_bytes - 1) / p.range_bytes);
   p.label_column = h->cfg.label_column;
   p.four = 4u;
+  p.sixteen = 16u;
   p.counts = s.d_counts;
   p.num_tiles = (p.num_ranges + kScanTile - 1) / kScanTile;
   p.tile_base = s.d_counts + static_cast<size_t>(kNumCounters) * p.num_ranges;
@@ -797,6 +798,7 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
   p.num_ranges = static_cast<uint32_t>((rq->nbytes + kNoAllocRangeBytes - 1) / kNoAllocRangeBytes);
   p.label_column = rq->label_column;
   p.four = 4u;
+  p.sixteen = 16u;
   p.counts = scratch->counts;
   p.num_tiles = (p.num_ranges + kScanTile - 1) / kScanTile;
   p.tile_base = scratch->tile_base;

@@ -69,6 +69,7 @@ struct WalkParams {
   uint32_t range_bytes;    /* multiple of kStepBytes */
   uint32_t num_ranges;
   int32_t label_column;    /* CSV */
+  uint32_t sixteen;        /* always 16, for the same reason as `four` below */
   uint32_t four;           /* always 4. Passed in so that the compiler cannot fold `acc * 4 + e`
                               into a shift-add on the (saturated) ALU pipe: as a run-time value
                               it stays an IMAD on the otherwise idle FMA pipe. */
@@ -154,7 +155,52 @@ template <int FMT>
 __device__ __forceinline__ uint32_t ClassEntry(uint32_t byte) {
   const bool eol = byte == '\n' || byte == '\r';
   const bool a = FMT == kCSV ? (eol || byte == ',') : IsDigitChar(byte);
-  return (a ? 1u : 0u) | (eol ? 2u : 0u);
+  uint32_t e = (a ? 1u : 0u) | (eol ? 2u : 0u);
+  if (FMT != kCSV) e |= (byte == ':' ? 4u : 0u) | (IsBlank(byte) ? 8u : 0u);
+  return e;
+}
+
+/* LibSVM / LibFM: four classes per byte (digit-run 1, EOL 2, ':' 4, blank 8), one nibble per byte:
+   m0 = bytes 0..7, m1 = bytes 8..15 of the lane's 16. */
+constexpr uint32_t kNibD = 0x11111111u;
+__device__ __forceinline__ void ClassifyLut4(const uint4 v, const uint8_t *lut, uint32_t sixteen,
+                                             uint32_t *m0, uint32_t *m1) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  uint32_t lo = 0, hi = 0;
+#pragma unroll
+  for (int j = 7; j >= 0; --j) {
+    lo = lo * sixteen + lut[__byte_perm(w[j >> 2], 0u, 0x4440u | (j & 3))];
+    hi = hi * sixteen + lut[__byte_perm(w[2 + (j >> 2)], 0u, 0x4440u | (j & 3))];
+  }
+  *m0 = lo;
+  *m1 = hi;
+}
+
+/* 8-bit byte mask -> 0xF in the nibble of every selected byte */
+__device__ __forceinline__ uint32_t SpreadNibbles8(uint32_t m) {
+  m = (m | (m << 12)) & 0x000f000fu;
+  m = (m | (m << 6)) & 0x03030303u;
+  m = (m | (m << 3)) & 0x11111111u;
+  return m * 15u;
+}
+
+/*
+ * Separator kind of a token from the classes of the two bytes in front of it (c = class nibble of
+ * byte -2 in the low half, of byte -1 in the high half):
+ *   3 line start   the byte before is an EOL
+ *   1 bound        "<digit-run byte>:"   -- separator is exactly ':'
+ *   2 unbound      "<digit-run byte><blank>" -- separator is exactly one blank
+ *   0 general      anything else: TokenGroup walks back over the separator
+ * Index = (EOL, ':', blank of byte -1) | digit-run of byte -2 << 3; two bits per entry.
+ */
+__device__ __forceinline__ uint32_t SeparatorKind(uint32_t c) {
+  const uint32_t idx = ((c >> 5) & 7u) | ((c & 1u) << 3);
+  /* idx: bit0 EOL, bit1 colon, bit2 blank, bit3 previous-previous is a digit-run byte.
+     EOL -> 3 regardless; colon&D -> 1; blank&D -> 2 */
+  constexpr uint32_t kTable =
+      (3u << 2) | (3u << 6) | (3u << 10) | (3u << 14) |            /* idx 1,3,5,7: EOL */
+      (3u << 18) | (1u << 20) | (3u << 22) | (2u << 24) | (3u << 26) | (3u << 30); /* idx 9..15 */
+  return (kTable >> (2u * idx)) & 3u;
 }
 
 __device__ __forceinline__ uint32_t ClassifyLut(const uint4 v, const uint8_t *lut, uint32_t four) {
@@ -348,50 +394,70 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
                                            WarpScratch<FMT> &ws, WalkState &st, uint32_t head,
                                            uint32_t count, int lane) {
   const bool active = lane < count;
-  const uint32_t at = active ? (ws.tokens[head + lane] >> 1) : 0u;
+  const uint32_t entry = active ? ws.tokens[head + lane] : 3u;
+  const uint32_t at = entry >> 2;
+  const uint32_t kind = entry & 3u;   /* separator kind, see SeparatorKind() */
 
-  /* ---- look back over the separator in front of this token ---- */
-  bool line_start = true;   /* separator contains an EOL (or the chunk starts here) */
-  bool bound = false;
+  /* ---- the separator in front of this token ---- */
+  bool line_start = kind == 3u;  /* separator contains an EOL (or the chunk starts here) */
+  bool bound = kind == 1u;
   bool qid_a = false, qid_b = false;     /* separator is [blank]*"qid:"... / [space]*"qid:"... */
   uint32_t qid_at_a = 0, qid_at_b = 0;   /* byte after that "qid:" */
-  if (active) {
-    const uint32_t kQid = (uint32_t(':') << 24) | (uint32_t('d') << 16) | (uint32_t('i') << 8) |
-                          uint32_t('q');
-    uint32_t first_nonblank = 0, window = 0;
-    bool in_a = false, in_b = false;
-    uint32_t q = at;
-    for (;;) {
-      if (q == 0u) break;               /* start of chunk: a line starts here */
-      --q;
-      const uint32_t c = txt.at(q);
-      if (IsEol(c)) break;
-      if (IsDigitChar(c)) {             /* previous token ends at q */
+  const bool general = active && kind == 0u;
+  if (__any_sync(0xffffffffu, general)) {
+    /* not one of the three common separators: walk back over it */
+    /* the one longer separator that well-formed ranking data has on every row,
+       "<digit-run byte> qid:" (libsvm_parser.h:66-75), is recognised without the walk */
+    bool walk = general;
+    if (FMT == kLibSVM && general && at >= 6u) {
+      if (txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
+          txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u))) {
         line_start = false;
-        bound = (first_nonblank == ':');
-        if (FMT == kLibSVM) {
-          if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; }
-          if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; }
-        }
-        break;
+        bound = false;            /* first non-blank of the separator is 'q' */
+        qid_a = qid_b = true;     /* one space, then "qid:": both probe variants match */
+        qid_at_a = qid_at_b = at;
+        walk = false;
       }
-      const bool space = (c == ' ');
-      const bool blank = space || c == '\t';
-      if (!blank) first_nonblank = c;
-      if (FMT == kLibSVM) {
-        /* leading-separator tracking for "qid:" (libsvm_parser.h:66-75): after `label` the
-           reference has skipped blanks, after `label:weight` only spaces */
-        if (blank) {
-          if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; in_a = true; }
-        } else {
-          in_a = false; qid_a = false;
+    }
+    if (walk) {
+      line_start = true;
+      const uint32_t kQid = (uint32_t(':') << 24) | (uint32_t('d') << 16) | (uint32_t('i') << 8) |
+                            uint32_t('q');
+      uint32_t first_nonblank = 0, window = 0;
+      bool in_a = false, in_b = false;
+      uint32_t q = at;
+      for (;;) {
+        if (q == 0u) break;               /* start of chunk: a line starts here */
+        --q;
+        const uint32_t c = txt.at(q);
+        if (IsEol(c)) break;
+        if (IsDigitChar(c)) {             /* previous token ends at q */
+          line_start = false;
+          bound = (first_nonblank == ':');
+          if (FMT == kLibSVM) {
+            if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; }
+            if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; }
+          }
+          break;
         }
-        if (space) {
-          if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; in_b = true; }
-        } else {
-          in_b = false; qid_b = false;
+        const bool space = (c == ' ');
+        const bool blank = space || c == '\t';
+        if (!blank) first_nonblank = c;
+        if (FMT == kLibSVM) {
+          /* leading-separator tracking for "qid:" (libsvm_parser.h:66-75): after `label` the
+             reference has skipped blanks, after `label:weight` only spaces */
+          if (blank) {
+            if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; in_a = true; }
+          } else {
+            in_a = false; qid_a = false;
+          }
+          if (space) {
+            if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; in_b = true; }
+          } else {
+            in_b = false; qid_b = false;
+          }
+          window = (window << 8) | c;
         }
-        window = (window << 8) | c;
       }
     }
   }
@@ -612,67 +678,59 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   if (begin < hi) {
     uint32_t fill = 0;          /* tokens waiting in ws.tokens */
     uint32_t end = prm.size;    /* tightened once the closing EOL is seen */
-    /* class bits (A | EOL << 1) of the byte before this step's first byte.
-       CSV: the EOL before `begin` is a separator and an EOL; LibSVM/LibFM: it is no digit */
-    uint32_t carry = FMT == kCSV ? 3u : 0u;
+    /* classes of the byte(s) before this step's first byte.  CSV: 2 bits (separator | EOL << 1)
+       of the previous byte -- the EOL before `begin` is both.  LibSVM/LibFM: class nibbles of
+       the previous two bytes -- an EOL (2) in the high nibble. */
+    uint32_t carry = FMT == kCSV ? 3u : 0x20u;
     bool done = false;
     uint32_t csv_fields = 0, csv_rows = 0; /* per-lane tallies of the CSV counting shortcut */
     for (uint32_t base = begin & ~uint32_t(kStepBytes - 1); !done; base += kStepBytes) {
       const uint32_t first_byte = base + 16u * lane;
       /* interior step: wholly owned, wholly inside the chunk, and too early to hold the EOL
-         that closes the region -- no masks, no bounds checks (14 of 16 steps of an 8 KiB range) */
+         that closes the region -- no masks, no bounds checks (30 of 32 steps of a 16 KiB range) */
       const bool interior = base >= begin && base + kStepBytes <= hi - 1u;
-      uint32_t cls;             /* interleaved class mask of my 16 bytes */
-      uint32_t keep = kEven;    /* owned bytes, on the even bits */
-      if (interior) {
-        cls = ClassifyLut(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), lut, prm.four);
-      } else {
-        cls = ClassifyLut(Load16(prm.text, prm.size, first_byte), lut, prm.four);
-        /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
-        const uint32_t closing = (cls >> 1) & Spread16(KeepMask(first_byte, hi - 1u, prm.size));
-        const uint32_t who = __ballot_sync(0xffffffffu, closing != 0u);
-        if (who != 0u) {
-          const int src = __ffs(who) - 1;
-          const uint32_t cs = __shfl_sync(0xffffffffu, closing, src);
-          end = base + 16u * src + ((__ffs(cs) - 1) >> 1) + 1u;
-          done = true;
-        } else if (base + kStepBytes >= prm.size) {
-          done = true;
+      if constexpr (FMT == kCSV) {
+        uint32_t cls;             /* interleaved class mask of my 16 bytes */
+        uint32_t keep = kEven;    /* owned bytes, on the even bits */
+        if (interior) {
+          cls = ClassifyLut(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), lut, prm.four);
+        } else {
+          cls = ClassifyLut(Load16(prm.text, prm.size, first_byte), lut, prm.four);
+          /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
+          const uint32_t closing = (cls >> 1) & Spread16(KeepMask(first_byte, hi - 1u, prm.size));
+          const uint32_t who = __ballot_sync(0xffffffffu, closing != 0u);
+          if (who != 0u) {
+            const int src = __ffs(who) - 1;
+            const uint32_t cs = __shfl_sync(0xffffffffu, closing, src);
+            end = base + 16u * src + ((__ffs(cs) - 1) >> 1) + 1u;
+            done = true;
+          } else if (base + kStepBytes >= prm.size) {
+            done = true;
+          }
+          keep = Spread16(KeepMask(first_byte, begin, end));
         }
-        keep = Spread16(KeepMask(first_byte, begin, end));
-      }
-
-      /* token starts in this lane's 16 bytes (even bits), CSV row starts likewise */
-      uint32_t up = __shfl_up_sync(0xffffffffu, cls >> 30, 1);
-      if (lane == 0) up = carry;
-      carry = __shfl_sync(0xffffffffu, cls >> 30, 31);
-      uint32_t starts, row_starts = 0;
-      if (FMT == kCSV) {
+        uint32_t up = __shfl_up_sync(0xffffffffu, cls >> 30, 1);
+        if (lane == 0) up = carry;
+        carry = __shfl_sync(0xffffffffu, cls >> 30, 31);
         /* a field starts after a comma or at a line start, unless that byte is an EOL
            (csv_parser.h:79-95: a trailing comma yields no extra column).  Unmasked classes are
            used for "what precedes me" so that the line start at `begin` is seen. */
         const uint32_t before = (cls << 2) | up;        /* classes of the previous byte */
         const uint32_t not_eol = ~(cls >> 1) & keep;
-        starts = before & not_eol;
-        row_starts = (before >> 1) & not_eol;
-      } else {
-        /* a digit run cannot cross `begin` or `end` (both follow an EOL byte) */
-        const uint32_t runs = cls & keep;
-        starts = runs & ~((runs << 2) | (up & 1u));
-      }
-      const uint32_t mine = __popc(starts);
-      if constexpr (FMT == kCSV && !EMIT) {
-        /* counting a CSV chunk needs no per-field work when the label is absent or is column 0
-           (every row then owns exactly one label field): rows and fields are popcounts */
-        if (prm.label_column <= 0) {
-          csv_fields += mine;
-          csv_rows += __popc(row_starts);
-          continue;
+        const uint32_t starts = before & not_eol;
+        const uint32_t row_starts = (before >> 1) & not_eol;
+        const uint32_t mine = __popc(starts);
+        if constexpr (!EMIT) {
+          /* counting a CSV chunk needs no per-field work when the label is absent or is column 0
+             (every row then owns exactly one label field): rows and fields are popcounts */
+          if (prm.label_column <= 0) {
+            csv_fields += mine;
+            csv_rows += __popc(row_starts);
+            continue;
+          }
         }
-      }
-      /* compact them, in file order, behind the tokens left from the previous step.
-         Queue entry = 2 * byte position (+ 1 for a CSV field that opens a row). */
-      {
+        /* compact the starts, in file order, behind the tokens left from the previous step.
+           Queue entry = 2 * byte position (+ 1 for a field that opens a row). */
         const uint32_t incl = WarpInclusiveSum(mine, lane);
         uint32_t slot = fill + incl - mine;
         uint32_t bits = starts;
@@ -680,9 +738,65 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
         while (bits != 0u) {
           const uint32_t b = __ffs(bits) - 1;     /* 2 * byte offset */
           bits &= bits - 1u;
-          uint32_t entry = first2 + b;
-          if (FMT == kCSV) entry += (row_starts >> b) & 1u;
-          ws.tokens[slot++] = entry;
+          ws.tokens[slot++] = first2 + b + ((row_starts >> b) & 1u);
+        }
+        fill += __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();
+      } else {
+        uint32_t m0, m1;                               /* class nibbles of bytes 0..7 / 8..15 */
+        uint32_t k0 = 0xffffffffu, k1 = 0xffffffffu;   /* owned bytes, as nibbles */
+        if (interior) {
+          ClassifyLut4(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), lut, prm.sixteen,
+                       &m0, &m1);
+        } else {
+          ClassifyLut4(Load16(prm.text, prm.size, first_byte), lut, prm.sixteen, &m0, &m1);
+          /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
+          const uint32_t cm = KeepMask(first_byte, hi - 1u, prm.size);
+          const uint32_t c0 = (m0 >> 1) & kNibD & SpreadNibbles8(cm & 0xffu);
+          const uint32_t c1 = (m1 >> 1) & kNibD & SpreadNibbles8(cm >> 8);
+          uint32_t off = 0xffffffffu;                  /* byte offset of my first closing EOL */
+          if (c0 != 0u) {
+            off = (__ffs(c0) - 1) >> 2;
+          } else if (c1 != 0u) {
+            off = 8u + ((__ffs(c1) - 1) >> 2);
+          }
+          const uint32_t who = __ballot_sync(0xffffffffu, off != 0xffffffffu);
+          if (who != 0u) {
+            const int src = __ffs(who) - 1;
+            end = base + 16u * src + __shfl_sync(0xffffffffu, off, src) + 1u;
+            done = true;
+          } else if (base + kStepBytes >= prm.size) {
+            done = true;
+          }
+          const uint32_t km = KeepMask(first_byte, begin, end);
+          k0 = SpreadNibbles8(km & 0xffu);
+          k1 = SpreadNibbles8(km >> 8);
+        }
+        uint32_t up = __shfl_up_sync(0xffffffffu, m1 >> 24, 1);   /* classes of bytes -2, -1 */
+        if (lane == 0) up = carry;
+        carry = __shfl_sync(0xffffffffu, m1 >> 24, 31);
+        /* digit-run bytes I own; a run cannot cross `begin` or `end` (both follow an EOL byte) */
+        const uint32_t d0 = m0 & kNibD & k0, d1 = m1 & kNibD & k1;
+        const uint32_t s0 = d0 & ~((d0 << 4) | ((up >> 4) & 1u));
+        const uint32_t s1 = d1 & ~((d1 << 4) | (d0 >> 28));
+        const uint32_t mine = __popc(s0) + __popc(s1);
+        /* compact the run starts.  Queue entry = 4 * byte position + separator kind, the kind read
+           off the (unmasked) classes of the two bytes in front of the token. */
+        const uint32_t incl = WarpInclusiveSum(mine, lane);
+        uint32_t slot = fill + incl - mine;
+        const uint32_t p_lo = up | (m0 << 8), p_mid = (m0 >> 24) | (m1 << 8), p_hi = m1 >> 24;
+        const uint32_t first4 = 4u * first_byte;
+        uint32_t bits = s0;
+        while (bits != 0u) {
+          const uint32_t b = __ffs(bits) - 1;     /* 4 * byte offset */
+          bits &= bits - 1u;
+          ws.tokens[slot++] = first4 + b + SeparatorKind(__funnelshift_r(p_lo, p_mid, b) & 0xffu);
+        }
+        bits = s1;
+        while (bits != 0u) {
+          const uint32_t b = __ffs(bits) - 1;
+          bits &= bits - 1u;
+          ws.tokens[slot++] = first4 + 32u + b + SeparatorKind(__funnelshift_r(p_mid, p_hi, b) & 0xffu);
         }
         fill += __shfl_sync(0xffffffffu, incl, 31);
         __syncwarp();

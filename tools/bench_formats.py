@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--mb", type=int, default=512)
     ap.add_argument("--range-bytes", type=int, default=0)
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--only", default="", help="substring of the shape name to run")
     args = ap.parse_args()
     peak = 6540.8
     try:
@@ -35,6 +36,8 @@ def main():
         pass
     out = []
     for name, kind, fmt, ib, lc in SHAPES:
+        if args.only and args.only not in name:
+            continue
         data, rows = datagen.generate(kind, 1, args.mb * 1000 * 1000)
         n = data.size
         pad = (-n) % 16
