@@ -43,7 +43,7 @@ class RowBlock(C.Structure):
                 ("offset", C.c_void_p), ("label", C.c_void_p), ("weight", C.c_void_p),
                 ("qid", C.c_void_p), ("field", C.c_void_p), ("index", C.c_void_p),
                 ("value", C.c_void_p), ("text_bytes", C.c_uint64), ("index_bytes", C.c_int32),
-                ("on_device", C.c_int32)]
+                ("on_device", C.c_int32), ("max_index", C.c_uint64), ("max_field", C.c_uint64)]
 
 
 class NoAllocRequest(C.Structure):

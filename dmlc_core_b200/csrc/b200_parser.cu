@@ -357,6 +357,8 @@ static void FillBlock(const b200p_handle h, const Slot &s, const Arrays &a, bool
   out->n_qid = sum.total[kQids];
   out->n_value = sum.total[kValues];
   out->n_field = h->cfg.format == B200P_FORMAT_LIBFM ? out->nnz : 0;
+  out->max_index = sum.max_index;
+  out->max_field = sum.max_field;
   if (out->rows == 0) return;
   out->offset = reinterpret_cast<const uint64_t *>(a.offset);
   out->label = a.label;
@@ -836,6 +838,8 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
   out->n_qid = sum.total[kQids];
   out->n_value = sum.total[kValues];
   out->n_field = need_field ? out->nnz : 0;
+  out->max_index = sum.max_index;
+  out->max_field = sum.max_field;
   if (sum.total[kRows] > rq->cap_rows || sum.total[kNnz] > rq->cap_nnz) {
     /* pass 2 wrote nothing; rows / nnz tell the caller how much room this chunk needs */
     if (errbuf != NULL && errlen != 0) {

@@ -59,6 +59,8 @@ constexpr int kRoleQueue = 64;         /* < 32 left over + <= 32 new per token g
 /* Result header written by ScanFinish (device memory, copied to the host per chunk). */
 struct ChunkSummary {
   unsigned long long total[kNumCounters];
+  unsigned long long max_index;  /* largest feature index / field id stored by pass 2: what */
+  unsigned long long max_field;  /* RowBlockContainer::Push tracks on the CPU (row_block.h:143,153) */
   unsigned int error;
   unsigned int ranges;
 };
@@ -310,6 +312,7 @@ struct WalkState {
   uint32_t n_label, n_weight, n_qid, n_index, n_value;
   uint32_t w_label, w_weight, w_qid, w_index, w_value;
   uint32_t error;
+  unsigned long long max_index, max_field; /* per lane; reduced when the walk ends */
 };
 
 template <typename IdxT>
@@ -358,11 +361,13 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
     const uint32_t take = min(st.n_index, 32u);
     bool neg = false;
     if (lane < take) {
-      StoreIdx<IdxT>(prm.index, st.w_index + lane,
-                     ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg));
+      const unsigned long long idx = ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg);
+      StoreIdx<IdxT>(prm.index, st.w_index + lane, idx);
+      st.max_index = max(st.max_index, idx);
       if (FMT == kLibFM) {
-        StoreIdx<IdxT>(prm.field, st.w_index + lane,
-                       ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg));
+        const unsigned long long fld = ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg);
+        StoreIdx<IdxT>(prm.field, st.w_index + lane, fld);
+        st.max_field = max(st.max_field, fld);
       }
     }
     if (neg) st.error |= kErrNegativeIndex; /* lane-local; OR-reduced at the end of the walk */
@@ -605,6 +610,7 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
             col - ((prm.label_column >= 0 && static_cast<int32_t>(col) > prm.label_column) ? 1u : 0u);
         prm.value[slot] = v;
         StoreIdx<IdxT>(prm.index, slot, idx);
+        st.max_index = max(st.max_index, static_cast<unsigned long long>(idx));
       }
     }
   }
@@ -662,6 +668,7 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   st.n_label = st.n_weight = st.n_qid = st.n_index = st.n_value = 0;
   st.w_label = st.w_weight = st.w_qid = st.w_index = st.w_value = 0;
   st.error = 0;
+  st.max_index = st.max_field = 0;
   if (EMIT) {
 #pragma unroll
     for (int c = 0; c < kNumCounters; ++c) {
@@ -838,6 +845,16 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   if (EMIT) {
     const uint32_t err = __reduce_or_sync(0xffffffffu, st.error);
     if (err != 0u && lane == 0) atomicOr(&prm.summary->error, err);
+    unsigned long long mi = st.max_index, mf = st.max_field;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      mi = max(mi, __shfl_xor_sync(0xffffffffu, mi, d));
+      mf = max(mf, __shfl_xor_sync(0xffffffffu, mf, d));
+    }
+    if (lane == 0) {
+      if (mi != 0ull) atomicMax(&prm.summary->max_index, mi);
+      if (FMT == kLibFM && mf != 0ull) atomicMax(&prm.summary->max_field, mf);
+    }
   } else {
     if (lane < kNumCounters) {
       uint32_t v = 0;
@@ -913,6 +930,8 @@ __global__ void __launch_bounds__(kScanTile) ScanFinish(uint32_t *tile_base, uin
     if (grand[kValues] != 0ull && grand[kValues] != grand[kNnz]) err |= kErrValueCount;
     summary->error = err;
     summary->ranges = num_ranges;
+    summary->max_index = 0ull;
+    summary->max_field = 0ull;
   }
 }
 

@@ -48,6 +48,10 @@ def load(path=None):
                                          C.POINTER(Block), C.POINTER(C.c_uint64), C.c_char_p,
                                          C.c_uint64]
     lib.dmlcb_rowiter_create.restype = C.c_void_p
+    lib.dmlcb_rowiter_next.argtypes = [C.c_void_p, C.POINTER(Block)]
+    lib.dmlcb_rowiter_next.restype = C.c_int
+    lib.dmlcb_rowiter_before_first.argtypes = [C.c_void_p]
+    lib.dmlcb_rowiter_before_first.restype = None
     lib.dmlcb_rowiter_free.argtypes = [C.c_void_p]
     lib.dmlcb_rowiter_free.restype = None
     lib.dmlcb_split_bytes.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_int, C.c_uint64,
@@ -152,19 +156,26 @@ def concat_blocks(parts, index_bytes):
     return out
 
 
-def row_iter(uri, part_index=0, num_parts=1, type_="libsvm", index_bytes=4):
-    """RowBlockIter<IndexType>::Create(...): returns (arrays of its single block, NumCol())."""
-    lib = load()
+def row_iter(uri, part_index=0, num_parts=1, type_="libsvm", index_bytes=4, lib=None, passes=1):
+    """RowBlockIter<IndexType>::Create(...) drained `passes` times (BeforeFirst in between):
+    returns (concatenated arrays of the last pass, NumCol(), number of blocks per pass)."""
+    lib = lib if lib is not None else load()
     b, ncol = Block(), C.c_uint64(0)
     err = C.create_string_buffer(2048)
     h = lib.dmlcb_rowiter_create(uri.encode(), part_index, num_parts, type_.encode(), index_bytes,
                                  C.byref(b), C.byref(ncol), err, 2048)
     if not h:
         raise DmlcError(err.value.decode())
-    out = _block_to_numpy(b, index_bytes)
-    out["error"] = 0
+    parts = []
+    for k in range(passes):
+        if k:
+            lib.dmlcb_rowiter_before_first(h)
+        parts = []
+        while lib.dmlcb_rowiter_next(h, C.byref(b)) == 1:
+            parts.append(_block_to_numpy(b, index_bytes))
+    out = concat_blocks(parts, index_bytes)
     lib.dmlcb_rowiter_free(h)
-    return out, int(ncol.value)
+    return out, int(ncol.value), len(parts)
 
 
 def split_bytes(uri, part_index, num_parts, mode=0, chunk_hint=0, cap=1 << 26):

@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <chrono>
 #include <future>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <limits>
@@ -59,7 +60,7 @@ class B200TextParser : public Parser<IndexType> {
  public:
   B200TextParser(InputSplit *source, int format, int label_column)
       : source_(source), text_(NULL), handle_(NULL),
-        bytes_read_(0), exhausted_(false) {
+        block_max_index_(0), bytes_read_(0), exhausted_(false) {
     std::memset(&block_, 0, sizeof(block_));
 #if B200_HAVE_TEXT_SPLIT
     text_ = dynamic_cast<TextSplit *>(source);
@@ -120,6 +121,7 @@ class B200TextParser : public Parser<IndexType> {
       Check(b200p_next(handle_, &b));
       bytes_read_ += b.text_bytes;
       if (b.rows == 0) continue;  /* chunks without rows are skipped (reference parser.h:33-38) */
+      block_max_index_ = b.max_index;
       block_.size = static_cast<size_t>(b.rows);
       block_.offset = reinterpret_cast<const size_t *>(b.offset);
       block_.label = b.label;
@@ -134,6 +136,8 @@ class B200TextParser : public Parser<IndexType> {
 
   virtual const RowBlock<IndexType> &Value(void) const { return block_; }
   virtual size_t BytesRead(void) const { return bytes_read_; }
+  /* largest feature index of the current block, reduced on the GPU while index[] was written */
+  uint64_t BlockMaxIndex() const { return block_max_index_; }
 
  private:
   /* keep the pipeline full: read chunks and enqueue them until `depth` are in flight */
@@ -243,6 +247,7 @@ class B200TextParser : public Parser<IndexType> {
 #endif
   b200p_handle handle_;
   RowBlock<IndexType> block_;
+  uint64_t block_max_index_;
   size_t bytes_read_;
   size_t chunk_bytes_;
   int depth_;
@@ -326,8 +331,18 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
   explicit InMemoryRowIter(Parser<IndexType> *parser) : at_head_(true), max_index_(0) {
     offset_.push_back(0);
     const double t0 = GetTime();
+    /* the B200 parser already knows each block's largest index (reduced on the GPU as the
+       array was written); any other parser gets the reference's per-element scan */
+    B200TextParser<IndexType> *gpu = dynamic_cast<B200TextParser<IndexType> *>(parser);
     try {
-      while (parser->Next()) Append(parser->Value());
+      while (parser->Next()) {
+        if (gpu != NULL) {
+          Append(parser->Value(), false);
+          max_index_ = std::max(max_index_, static_cast<IndexType>(gpu->BlockMaxIndex()));
+        } else {
+          Append(parser->Value(), true);
+        }
+      }
     } catch (...) {
       delete parser;
       throw;
@@ -357,14 +372,16 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
   virtual size_t NumCol(void) const { return static_cast<size_t>(max_index_) + 1; }
 
  private:
-  void Append(const RowBlock<IndexType> &b) {
+  void Append(const RowBlock<IndexType> &b, bool scan_max) {
     const size_t base = b.offset[0], nnz = b.offset[b.size] - base, shift = offset_.back();
     label_.insert(label_.end(), b.label, b.label + b.size);
     if (b.weight != NULL) weight_.insert(weight_.end(), b.weight, b.weight + b.size);
     if (b.qid != NULL) qid_.insert(qid_.end(), b.qid, b.qid + b.size);
     if (b.field != NULL) field_.insert(field_.end(), b.field + base, b.field + base + nnz);
     index_.insert(index_.end(), b.index + base, b.index + base + nnz);
-    for (size_t i = 0; i < nnz; ++i) max_index_ = std::max(max_index_, b.index[base + i]);
+    if (scan_max) {
+      for (size_t i = 0; i < nnz; ++i) max_index_ = std::max(max_index_, b.index[base + i]);
+    }
     if (b.value != NULL) value_.insert(value_.end(), b.value + base, b.value + base + nnz);
     for (size_t i = 1; i <= b.size; ++i) offset_.push_back(shift + b.offset[i] - base);
   }
@@ -377,16 +394,176 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
   std::vector<IndexType> field_, index_;
 };
 
+/*
+ * RowBlockIter back-end with a disk cache of parsed pages ("uri#cachefile"): reference
+ * DiskRowIter, src/data/disk_row_iter.h:27-141.  The page format is the reference's
+ * RowBlockContainer::Save (src/data/row_block.h:189-201 over serializer.h:105-112): seven arrays,
+ * each a u64 element count followed by the raw elements (offset u64, label f32, weight f32,
+ * qid u64, field I, index I, value f32), then max_field and max_index as IndexType.  Caches
+ * written here load in the reference and the other way round; a page is closed once it holds
+ * >= 64 MiB of arrays (disk_row_iter.h:32,123).
+ */
+template <typename IndexType>
+class CachedRowIter : public RowBlockIter<IndexType> {
+ public:
+  static const size_t kPageSize = 64UL << 20UL;
+
+  /* true when `cache_file` exists and starts with a readable page */
+  static bool Usable(const std::string &cache_file) {
+    std::FILE *f = std::fopen(cache_file.c_str(), "rb");
+    if (f == NULL) return false;
+    uint64_t n = 0;
+    const bool ok = std::fread(&n, sizeof(n), 1, f) == 1 && n >= 1;
+    std::fclose(f);
+    return ok;
+  }
+
+  /* parser == NULL: the cache must already exist */
+  CachedRowIter(Parser<IndexType> *parser, const std::string &cache_file)
+      : cache_file_(cache_file), fi_(NULL), num_col_(0) {
+    if (parser != NULL) {
+      try {
+        Build(parser);
+      } catch (...) {
+        delete parser;
+        throw;
+      }
+      delete parser;
+    }
+    fi_ = std::fopen(cache_file_.c_str(), "rb");
+    CHECK(fi_ != NULL) << "failed to build cache file " << cache_file_;
+    if (parser == NULL) {
+      /* NumCol of an existing cache: the largest max_index over its pages */
+      while (LoadPage()) num_col_ = std::max(num_col_, static_cast<size_t>(page_max_index_) + 1);
+      BeforeFirst();
+    }
+  }
+  virtual ~CachedRowIter() {
+    if (fi_ != NULL) std::fclose(fi_);
+  }
+  virtual void BeforeFirst(void) { std::fseek(fi_, 0, SEEK_SET); }
+  virtual bool Next(void) {
+    if (!LoadPage()) return false;
+    block_.size = label_.size();
+    block_.offset = BeginPtr(offset_);
+    block_.label = BeginPtr(label_);
+    block_.weight = BeginPtr(weight_);
+    block_.qid = BeginPtr(qid_);
+    block_.field = BeginPtr(field_);
+    block_.index = BeginPtr(index_);
+    block_.value = BeginPtr(value_);
+    return true;
+  }
+  virtual const RowBlock<IndexType> &Value(void) const { return block_; }
+  virtual size_t NumCol(void) const { return num_col_; }
+
+ private:
+  template <typename T>
+  static void WriteVec(std::FILE *f, const std::vector<T> &v) {
+    const uint64_t n = v.size();
+    CHECK(std::fwrite(&n, sizeof(n), 1, f) == 1) << "cache write failed";
+    if (n != 0) CHECK(std::fwrite(&v[0], sizeof(T), v.size(), f) == v.size()) << "cache write failed";
+  }
+  template <typename T>
+  static bool ReadVec(std::FILE *f, std::vector<T> *v) {
+    uint64_t n = 0;
+    if (std::fread(&n, sizeof(n), 1, f) != 1) return false;
+    v->resize(static_cast<size_t>(n));
+    return n == 0 || std::fread(&(*v)[0], sizeof(T), v->size(), f) == v->size();
+  }
+  size_t MemCost() const {
+    return offset_.size() * sizeof(size_t) + (label_.size() + weight_.size() + value_.size()) * sizeof(real_t) +
+           qid_.size() * sizeof(size_t) + (field_.size() + index_.size()) * sizeof(IndexType);
+  }
+  void ClearPage() {
+    offset_.assign(1, 0);
+    label_.clear(); weight_.clear(); qid_.clear(); field_.clear(); index_.clear(); value_.clear();
+    page_max_index_ = 0;
+    page_max_field_ = 0;
+  }
+  void SavePage(std::FILE *fo) {
+    WriteVec(fo, offset_); WriteVec(fo, label_); WriteVec(fo, weight_); WriteVec(fo, qid_);
+    WriteVec(fo, field_); WriteVec(fo, index_); WriteVec(fo, value_);
+    CHECK(std::fwrite(&page_max_field_, sizeof(IndexType), 1, fo) == 1) << "cache write failed";
+    CHECK(std::fwrite(&page_max_index_, sizeof(IndexType), 1, fo) == 1) << "cache write failed";
+    num_col_ = std::max(num_col_, static_cast<size_t>(page_max_index_) + 1);
+  }
+  bool LoadPage() {
+    if (!ReadVec(fi_, &offset_)) return false;
+    CHECK(ReadVec(fi_, &label_) && ReadVec(fi_, &weight_) && ReadVec(fi_, &qid_) && ReadVec(fi_, &field_) &&
+          ReadVec(fi_, &index_) && ReadVec(fi_, &value_) &&
+          std::fread(&page_max_field_, sizeof(IndexType), 1, fi_) == 1 &&
+          std::fread(&page_max_index_, sizeof(IndexType), 1, fi_) == 1)
+        << "Bad RowBlock format";
+    return true;
+  }
+  void Build(Parser<IndexType> *parser) {
+    std::FILE *fo = std::fopen(cache_file_.c_str(), "wb");
+    CHECK(fo != NULL) << "cannot write cache file " << cache_file_;
+    B200TextParser<IndexType> *gpu = dynamic_cast<B200TextParser<IndexType> *>(parser);
+    const double t0 = GetTime();
+    ClearPage();
+    try {
+      while (parser->Next()) {
+        const RowBlock<IndexType> &b = parser->Value();
+        const size_t base = b.offset[0], nnz = b.offset[b.size] - base, shift = offset_.back();
+        label_.insert(label_.end(), b.label, b.label + b.size);
+        if (b.weight != NULL) weight_.insert(weight_.end(), b.weight, b.weight + b.size);
+        if (b.qid != NULL) qid_.insert(qid_.end(), b.qid, b.qid + b.size);
+        if (b.field != NULL) {
+          field_.insert(field_.end(), b.field + base, b.field + base + nnz);
+          for (size_t i = 0; i < nnz; ++i) page_max_field_ = std::max(page_max_field_, b.field[base + i]);
+        }
+        index_.insert(index_.end(), b.index + base, b.index + base + nnz);
+        if (gpu != NULL) {
+          page_max_index_ = std::max(page_max_index_, static_cast<IndexType>(gpu->BlockMaxIndex()));
+        } else {
+          for (size_t i = 0; i < nnz; ++i) page_max_index_ = std::max(page_max_index_, b.index[base + i]);
+        }
+        if (b.value != NULL) value_.insert(value_.end(), b.value + base, b.value + base + nnz);
+        for (size_t i = 1; i <= b.size; ++i) offset_.push_back(shift + b.offset[i] - base);
+        if (MemCost() >= kPageSize) {
+          SavePage(fo);
+          ClearPage();
+        }
+      }
+      if (!label_.empty()) SavePage(fo);
+    } catch (...) {
+      std::fclose(fo);
+      std::remove(cache_file_.c_str());
+      throw;
+    }
+    std::fclose(fo);
+    const double dt = GetTime() - t0;
+    LOG(INFO) << "finish reading at " << (parser->BytesRead() >> 20UL) / (dt > 0 ? dt : 1e-9) << " MB/sec";
+  }
+
+  std::string cache_file_;
+  std::FILE *fi_;
+  size_t num_col_;
+  IndexType page_max_index_, page_max_field_;
+  RowBlock<IndexType> block_;
+  std::vector<size_t> offset_;
+  std::vector<real_t> label_, weight_, value_;
+  std::vector<uint64_t> qid_;
+  std::vector<IndexType> field_, index_;
+};
+
+/* reference CreateIter_, src/data.cc:87-107: "#cachefile" selects the disk-backed iterator */
 template <typename IndexType>
 RowBlockIter<IndexType> *CreateIterImpl(const char *uri, unsigned part_index, unsigned num_parts,
                                         const char *type) {
   UriSpec spec(uri, part_index, num_parts);
-  CHECK(spec.cache_file.empty())
-      << "#cachefile (DiskRowIter) is not provided by dmlc_core_b200 yet";
-  /* strip the cache suffix only; the ?args travel on to the parser factory */
-  std::string no_cache = uri;
+  std::string no_cache = uri;   /* the ?args travel on to the parser factory */
   const size_t hash = no_cache.find('#');
   if (hash != std::string::npos) no_cache.resize(hash);
+  if (!spec.cache_file.empty()) {
+    if (CachedRowIter<IndexType>::Usable(spec.cache_file)) {
+      return new CachedRowIter<IndexType>(NULL, spec.cache_file);  /* later epochs skip parsing */
+    }
+    return new CachedRowIter<IndexType>(
+        CreateParserImpl<IndexType>(no_cache.c_str(), part_index, num_parts, type), spec.cache_file);
+  }
   return new InMemoryRowIter<IndexType>(CreateParserImpl<IndexType>(no_cache.c_str(), part_index, num_parts, type));
 }
 

@@ -105,8 +105,8 @@ void dmlcb_parser_free(void *handle) {
   delete h;
 }
 
-/* RowBlockIter<I>::Create + NumCol (reference test/dataiter_test.cc); the single block stays
-   valid until dmlcb_rowiter_free */
+/* RowBlockIter<I>::Create + NumCol (reference test/dataiter_test.cc); blocks come from
+   dmlcb_rowiter_next and stay valid until the next call on the handle */
 struct dmlcb_rowiter {
   dmlc::RowBlockIter<uint32_t> *i32;
   dmlc::RowBlockIter<uint64_t> *i64;
@@ -122,12 +122,10 @@ void *dmlcb_rowiter_create(const char *uri, unsigned part, unsigned nparts, cons
     if (index_bytes == 8) {
       h->i64 = dmlc::RowBlockIter<uint64_t>::Create(uri, part, nparts, type);
       h->i64->BeforeFirst();
-      if (h->i64->Next()) Export(h->i64->Value(), out);
       *num_col = h->i64->NumCol();
     } else {
       h->i32 = dmlc::RowBlockIter<uint32_t>::Create(uri, part, nparts, type);
       h->i32->BeforeFirst();
-      if (h->i32->Next()) Export(h->i32->Value(), out);
       *num_col = h->i32->NumCol();
     }
   } catch (const std::exception &e) {
@@ -138,6 +136,24 @@ void *dmlcb_rowiter_create(const char *uri, unsigned part, unsigned nparts, cons
     return NULL;
   }
   return h;
+}
+
+/* 1: another block was produced; 0: end */
+int dmlcb_rowiter_next(void *handle, dmlcb_block *out) {
+  dmlcb_rowiter *h = static_cast<dmlcb_rowiter *>(handle);
+  if (h->i64 != NULL) {
+    if (!h->i64->Next()) return 0;
+    Export(h->i64->Value(), out);
+  } else {
+    if (!h->i32->Next()) return 0;
+    Export(h->i32->Value(), out);
+  }
+  return 1;
+}
+
+void dmlcb_rowiter_before_first(void *handle) {
+  dmlcb_rowiter *h = static_cast<dmlcb_rowiter *>(handle);
+  if (h->i64 != NULL) h->i64->BeforeFirst(); else h->i32->BeforeFirst();
 }
 
 void dmlcb_rowiter_free(void *handle) {

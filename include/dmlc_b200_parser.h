@@ -82,6 +82,11 @@ typedef struct b200p_rowblock {
   uint64_t text_bytes; /* size of the chunk this block came from (-> Parser::BytesRead) */
   int32_t index_bytes;
   int32_t on_device;   /* 1: pointers are device memory, 0: pinned host memory */
+  /* largest value in index[] / field[] (0 when empty), reduced on the GPU while the arrays are
+     written: what RowBlockContainer::Push accumulates per element on the CPU
+     (src/data/row_block.h:143,153) and RowBlockIter::NumCol() reports (basic_row_iter.h:44) */
+  uint64_t max_index;
+  uint64_t max_field;
 } b200p_rowblock;
 
 /* Replaces: new LibSVMParser<I>(source, nthread) etc. (src/data.cc:21-60). Allocates the

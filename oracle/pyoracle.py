@@ -192,6 +192,9 @@ class Reference(_Checker):
                                          C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         lib.refshim_time_uri.restype = C.c_double
         lib.refshim_max_threads.restype = C.c_int
+        lib.refshim_iter_uri.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_char_p, C.c_int,
+                                         C.POINTER(_Result), C.POINTER(C.c_uint64)]
+        lib.refshim_iter_uri.restype = None
 
     def parse_uri(self, uri, part=0, nparts=1, type_="libsvm", index_bytes=4):
         r = _Result()
@@ -200,6 +203,16 @@ class Reference(_Checker):
         out = _to_dict(r)
         self._free(C.byref(r))
         return out
+
+    def iter_uri(self, uri, part=0, nparts=1, type_="libsvm", index_bytes=4):
+        """RowBlockIter<I>::Create drained once -> (arrays, NumCol)."""
+        r = _Result()
+        ncol = C.c_uint64(0)
+        self.lib.refshim_iter_uri(uri.encode(), part, nparts, type_.encode(), index_bytes,
+                                  C.byref(r), C.byref(ncol))
+        out = _to_dict(r)
+        self._free(C.byref(r))
+        return out, int(ncol.value)
 
     def split_bytes(self, uri, part, nparts, cap):
         buf = C.create_string_buffer(cap + 1)

@@ -168,6 +168,25 @@ void ParseBuffer(int format, int label_column, const char *buf, size_t len, orac
   out->bytes_read = len;
 }
 
+/* RowBlockIter<I>::Create(uri, ...) drained once (uri may carry "#cachefile": the reference's
+   DiskRowIter, src/data/disk_row_iter.h). *num_col receives NumCol(). */
+template <typename I>
+void IterUri(const char *uri, unsigned part, unsigned nparts, const char *type,
+                    oracle_result *out, uint64_t *num_col) {
+  Accum<I> acc;
+  dmlc::RowBlockIter<I> *it = NULL;
+  try {
+    it = dmlc::RowBlockIter<I>::Create(uri, part, nparts, type);
+    it->BeforeFirst();
+    while (it->Next()) acc.Add(it->Value());
+    *num_col = it->NumCol();
+  } catch (const std::exception &e) {
+    SetError(out, e.what());
+  }
+  delete it;
+  Export(acc, out);
+}
+
 }  // namespace
 
 extern "C" {
@@ -189,6 +208,17 @@ void refshim_parse_buffer(int format, int index_bytes, int label_column, const c
     ParseBuffer<uint64_t>(format, label_column, buf, len, out);
   } else {
     ParseBuffer<uint32_t>(format, label_column, buf, len, out);
+  }
+}
+
+void refshim_iter_uri(const char *uri, unsigned part, unsigned nparts, const char *type,
+                      int index_bytes, oracle_result *out, uint64_t *num_col) {
+  std::memset(out, 0, sizeof(*out));
+  *num_col = 0;
+  if (index_bytes == 8) {
+    IterUri<uint64_t>(uri, part, nparts, type, out, num_col);
+  } else {
+    IterUri<uint32_t>(uri, part, nparts, type, out, num_col);
   }
 }
 

@@ -157,3 +157,29 @@ def test_true_dropin_build_against_reference_headers(hostapi):
         except hostapi.DmlcError as e:
             got = {"error": 1, "errmsg": str(e)}
         assert same_rowblocks(_trim_hidden_lengths(got, exp), exp) is None, case["name"]
+
+
+def test_disk_cache_round_trip_with_the_reference(hostapi, reference, oracle, tmp_path, monkeypatch):
+    """"uri#cachefile" (SURVEY 8f-3): pages written here in the reference's RowBlockContainer::Save
+    layout are read back by the reference's own DiskRowIter, and a second Create here replays the
+    cache without parsing."""
+    from dmlc_core_b200 import datagen
+    monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
+    for kind, fmt, ib, lc in (("libsvm", "libsvm", 4, -1), ("libfm", "libfm", 8, -1), ("csv", "csv", 4, 0)):
+        data, rows = datagen.generate(kind, 15, 3 << 20)
+        f = tmp_path / (kind + ".txt")
+        f.write_bytes(data.tobytes())
+        cache = tmp_path / (kind + ".cache")
+        args = "?format=csv&label_column=0" if fmt == "csv" else ""
+        uri = "%s%s#%s" % (f, args, cache)
+        exp = oracle.parse_buffer(fmt, data.tobytes(), ib, lc)
+        got, ncol, nblocks = hostapi.row_iter(uri, 0, 1, fmt, ib)          # parses on the GPU, writes pages
+        assert same_rowblocks(got, exp) is None
+        assert ncol == int(exp["index"].max()) + 1
+        size = os.path.getsize(cache)
+        theirs, _ = reference.iter_uri(uri, 0, 1, fmt, ib)                  # the reference replays OUR cache
+        assert same_rowblocks(theirs, exp) is None
+        f.write_bytes(b"")                                                   # text gone: must come from the cache
+        again, ncol2, _ = hostapi.row_iter(uri, 0, 1, fmt, ib, passes=2)
+        assert same_rowblocks(again, exp) is None and ncol2 == ncol
+        assert os.path.getsize(cache) == size

@@ -145,6 +145,22 @@ def test_corpus_streaming(cuda_lib, oracle, kind, fmt, ib, lc):
     assert same_rowblocks(got, exp) is None
 
 
+@pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA)
+def test_max_index_is_reduced_on_the_gpu(cuda_lib, oracle, kind, fmt, ib, lc):
+    """b200p_rowblock.max_index / max_field = what RowBlockContainer::Push would accumulate."""
+    from dmlc_core_b200 import datagen
+    from gpu_util import to_device
+    data, _ = datagen.generate(kind, 9, 2 << 20)
+    exp = oracle.parse_buffer(fmt, data.tobytes(), ib, lc)
+    p = _parser(cuda_lib, fmt, ib, lc)
+    t, n = to_device(data)
+    for _ in range(2):       # second call: the summary must have been reset
+        blk = p.parse_device(t.data_ptr(), n)
+        assert blk.max_index == int(exp["index"].max())
+        assert blk.max_field == (int(exp["field"].max()) if len(exp["field"]) else 0)
+    p.close()
+
+
 def test_edge_inputs(cuda_lib, oracle):
     cases = [
         ("libsvm", b""), ("libsvm", b"\n"), ("libsvm", b"\n\n\r\n"), ("libsvm", b"1"), ("libsvm", b"1 2:3"),

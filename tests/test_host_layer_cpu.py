@@ -100,3 +100,23 @@ def test_create_errors_match_reference_behaviour(hostapi, tmp_path):
     if not torch.cuda.is_available():
         with pytest.raises(hostapi.DmlcError, match="no CPU path|cannot create"):
             hostapi.CppParser(str(f) + "?format=csv&label_column=0", 0, 1, "auto")
+
+
+def test_cache_written_by_the_reference_loads_here(hostapi, reference, oracle, tmp_path):
+    """"uri#cachefile": a page cache built by the reference's DiskRowIter
+    (src/data/disk_row_iter.h:111-141, RowBlockContainer::Save row_block.h:189-201) is read back by
+    this package's RowBlockIter without parsing anything (no GPU involved)."""
+    from dmlc_core_b200 import datagen
+    from oracle.pyoracle import same_rowblocks
+    for kind, fmt, ib in (("libsvm", "libsvm", 4), ("libfm", "libfm", 8), ("libsvm_qid", "libsvm", 4)):
+        data, rows = datagen.generate(kind, 14, 600 << 10)
+        f = tmp_path / (kind + ".txt")
+        f.write_bytes(data.tobytes())
+        cache = tmp_path / (kind + ".cache")
+        uri = "%s#%s" % (f, cache)
+        ref_blocks, ref_ncol = reference.iter_uri(uri, 0, 1, fmt, ib)     # builds the cache
+        assert os.path.getsize(cache) > 0 and ref_blocks["error"] == 0
+        got, ncol, _ = hostapi.row_iter(uri, 0, 1, fmt, ib, passes=2)
+        exp = oracle.parse_buffer(fmt, data.tobytes(), ib)
+        assert same_rowblocks(got, exp) is None
+        assert ncol == int(exp["index"].max()) + 1
