@@ -111,7 +111,7 @@ def test_row_block_iter_numcol(hostapi, oracle, tmp_path):
     f = tmp_path / "it.svm"
     f.write_bytes(data.tobytes())
     exp = oracle.parse_buffer("libsvm", data.tobytes(), 4)
-    got, ncol = hostapi.row_iter(str(f), 0, 1, "libsvm", 4)
+    got, ncol, _ = hostapi.row_iter(str(f), 0, 1, "libsvm", 4)
     assert same_rowblocks(got, exp) is None
     assert ncol == int(exp["index"].max()) + 1
 
