@@ -330,7 +330,7 @@ def main():
         h_out = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
         s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
 
-        def copies(up, down, reps=4):
+        def link_rate(up, down, reps=4):
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             for _ in range(reps):
@@ -343,9 +343,9 @@ def main():
             torch.cuda.synchronize()
             return reps * nb / (time.perf_counter() - t0) / GB
 
-        copies(True, True, 1)
-        link = {"h2d_only_GBps": copies(True, False), "d2h_only_GBps": copies(False, True),
-                "h2d_with_concurrent_d2h_GBps": copies(True, True),
+        link_rate(True, True, 1)
+        link = {"h2d_only_GBps": link_rate(True, False), "d2h_only_GBps": link_rate(False, True),
+                "h2d_with_concurrent_d2h_GBps": link_rate(True, True),
                 "how": "pinned cudaMemcpyAsync of %d MiB blocks, 4 reps" % (nb >> 20)}
         del d_tmp, h_out
 
