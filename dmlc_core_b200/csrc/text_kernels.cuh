@@ -16,15 +16,18 @@
  * The chunk is cut into fixed byte ranges; a warp owns the lines that START inside its range
  * (the reference slices a chunk the same way for its OpenMP team, text_parser.h:104-118), so no
  * parsing state ever crosses a range.  Inside a range the warp streams 512-byte steps: every
- * lane loads 16 contiguous bytes (one coalesced 512 B request per warp), classifies them with
- * SWAR arithmetic into digit-run / end-of-line bit masks, and the starts of digit runs
- * ("tokens") are compacted into a per-warp queue in shared memory.  Tokens are then handled 32
- * at a time, one per lane: a short backward look at the separator decides whether the token is
- * bound by ':' to the previous one, and warp ballots + popc/clz turn those flags into chain
- * positions, roles (label / weight / qid / field / index / value), row ids and output slots --
- * the exact pairing rules of ParsePair / ParseTriple (reference src/data/strtonum.h:227-303).
- * Tokens of one role are queued again so that conversion always runs with 32 busy lanes doing
- * the same arithmetic, and every store is 32 consecutive elements of one CSR array.
+ * lane loads 16 contiguous bytes (one coalesced 512 B request per warp) and classifies them
+ * through a 256-byte table in shared memory (PRMT + LDS.U8 + IMAD per byte: the logic/shift ALU
+ * pipe is what bounds these kernels, so the work is spread over the LSU and FMA pipes) into
+ * interleaved class masks; the starts of digit runs ("tokens"; CSV: field starts) are compacted
+ * into a per-warp queue in shared memory, each tagged with the kind of separator in front of
+ * it.  Tokens are then handled 32 at a time, one per lane: warp ballots + popc/clz turn "bound
+ * by ':' to the previous token" / "starts a line" into chain positions, roles (label / weight /
+ * qid / field / index / value), row ids and output slots -- the exact pairing rules of
+ * ParsePair / ParseTriple (reference src/data/strtonum.h:227-303); only unusual separators are
+ * walked byte by byte.  Tokens of one role are queued again so that conversion always runs with
+ * 32 busy lanes doing the same arithmetic, and every store is 32 consecutive elements of one
+ * CSR array.
  */
 #ifndef DMLC_CORE_B200_TEXT_KERNELS_CUH_
 #define DMLC_CORE_B200_TEXT_KERNELS_CUH_
@@ -92,54 +95,21 @@ struct WalkParams {
   unsigned long long cap_nnz;
 };
 
-/* ---------------------------------------------------------------- SWAR byte classes -------- */
-/* All helpers take xm = word & 0x7f7f7f7f and return a word whose bit 7 of each byte is the
-   predicate; bytes >= 0x80 are removed by the caller with & ~word. */
+/* ------------------------------------------------------------- SWAR end-of-line scan -------- */
+/* Used only by FindEol (the short forward look for a range's first line start); the walks
+   themselves classify bytes through the shared-memory table below.
+   xm = word & 0x7f7f7f7f; bit 7 of each result byte is the predicate; bytes >= 0x80 are removed
+   with & ~word. */
 __device__ __forceinline__ uint32_t ByteEq(uint32_t xm, uint32_t c) {
   return ~((xm ^ (c * 0x01010101u)) + 0x7f7f7f7fu);
-}
-__device__ __forceinline__ uint32_t ByteGe(uint32_t xm, uint32_t c) {
-  return xm + ((0x80u - c) * 0x01010101u);
 }
 /* bit 7 of each byte -> 4 adjacent bits */
 __device__ __forceinline__ uint32_t Gather4(uint32_t m) {
   return (((m & 0x80808080u) >> 7) * 0x00204081u >> 21) & 0xFu;
 }
-
-__device__ __forceinline__ uint32_t WordDigitChar(uint32_t w) {
-  const uint32_t xm = w & 0x7f7f7f7fu;
-  const uint32_t in_range = ByteGe(xm, 0x2Bu) & ~ByteGe(xm, 0x3Au);      /* '+' .. '9' */
-  const uint32_t not_sep = ~(ByteEq(xm, ',') | ByteEq(xm, '/'));
-  const uint32_t is_e = ~(((xm | 0x20202020u) ^ 0x65656565u) + 0x7f7f7f7fu);
-  return ((in_range & not_sep) | is_e) & ~w;
-}
 __device__ __forceinline__ uint32_t WordEol(uint32_t w) {
   const uint32_t xm = w & 0x7f7f7f7fu;
   return (ByteEq(xm, '\n') | ByteEq(xm, '\r')) & ~w;
-}
-__device__ __forceinline__ uint32_t WordComma(uint32_t w) {
-  const uint32_t xm = w & 0x7f7f7f7fu;
-  return ByteEq(xm, ',') & ~w;
-}
-
-struct Masks16 {
-  uint32_t a;  /* digit-run bytes (LibSVM/LibFM) or commas (CSV) */
-  uint32_t eol;
-};
-
-template <int FMT>
-__device__ __forceinline__ Masks16 Classify(const uint4 v) {
-  Masks16 m;
-  if (FMT == kCSV) {
-    m.a = Gather4(WordComma(v.x)) | (Gather4(WordComma(v.y)) << 4) |
-          (Gather4(WordComma(v.z)) << 8) | (Gather4(WordComma(v.w)) << 12);
-  } else {
-    m.a = Gather4(WordDigitChar(v.x)) | (Gather4(WordDigitChar(v.y)) << 4) |
-          (Gather4(WordDigitChar(v.z)) << 8) | (Gather4(WordDigitChar(v.w)) << 12);
-  }
-  m.eol = Gather4(WordEol(v.x)) | (Gather4(WordEol(v.y)) << 4) | (Gather4(WordEol(v.z)) << 8) |
-          (Gather4(WordEol(v.w)) << 12);
-  return m;
 }
 
 /*
