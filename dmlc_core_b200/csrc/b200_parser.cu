@@ -89,6 +89,24 @@ struct b200p_parser_s {
 
 static thread_local std::string g_create_error;
 
+/* Every entry point works on its handle's device but leaves the caller's current device as it
+   found it (the host program may be driving other GPUs from the same thread). */
+class DeviceScope {
+ public:
+  explicit DeviceScope(int device) : previous_(-1), status_(cudaSuccess) {
+    if (cudaGetDevice(&previous_) != cudaSuccess) previous_ = -1;
+    if (previous_ != device) status_ = cudaSetDevice(device);
+    else previous_ = -1;
+  }
+  ~DeviceScope() {
+    if (previous_ >= 0) cudaSetDevice(previous_);
+  }
+  cudaError_t status() const { return status_; }
+ private:
+  int previous_;
+  cudaError_t status_;
+};
+
 #define CUDA_TRY(h, expr)                                                              \
   do {                                                                                 \
     cudaError_t e_ = (expr);                                                           \
@@ -442,7 +460,8 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
     delete h;
     return B200P_E_CUDA;
   }
-  e = cudaSetDevice(config->device);
+  DeviceScope on_device(config->device);
+  e = on_device.status();
   int rc = B200P_OK;
   if (e != cudaSuccess) {
     g_create_error = std::string("b200p_create: cudaSetDevice failed: ") + cudaGetErrorString(e);
@@ -462,7 +481,7 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
 
 void b200p_destroy(b200p_handle h) {
   if (h == NULL) return;
-  cudaSetDevice(h->cfg.device);
+  DeviceScope on_device(h->cfg.device);
   ProfCollect(h);
   for (size_t i = 0; i < h->slots.size(); ++i) DestroySlot(&h->slots[i]);
   DestroySlot(&h->resident);
@@ -473,6 +492,7 @@ uint64_t b200p_launch_count(b200p_handle h) { return h != NULL ? h->launches : 0
 
 int b200p_set_profiling(b200p_handle h, int on) {
   if (h == NULL) return B200P_E_INVALID;
+  DeviceScope on_device(h->cfg.device);
   ProfCollect(h);
   h->profiling = on != 0;
   for (int k = 0; k < 3; ++k) { h->kernel_ms[k] = 0.0; h->kernel_launches[k] = 0; }
@@ -481,7 +501,7 @@ int b200p_set_profiling(b200p_handle h, int on) {
 
 int b200p_kernel_time(b200p_handle h, int kernel, double *total_ms, uint64_t *launches) {
   if (h == NULL || kernel < 0 || kernel > 2) return B200P_E_INVALID;
-  cudaSetDevice(h->cfg.device);
+  DeviceScope on_device(h->cfg.device);
   ProfCollect(h); /* waits for the recorded events */
   if (total_ms != NULL) *total_ms = h->kernel_ms[kernel];
   if (launches != NULL) *launches = h->kernel_launches[kernel];
@@ -493,7 +513,8 @@ int b200p_parse_device_async(b200p_handle h, const void *d_text, uint64_t nbytes
   if (h == NULL) return B200P_E_INVALID;
   if (nbytes > B200P_MAX_CHUNK_BYTES) return Fail(h, B200P_E_INVALID, "chunk larger than B200P_MAX_CHUNK_BYTES");
   if ((reinterpret_cast<uintptr_t>(d_text) & 15u) != 0) return Fail(h, B200P_E_INVALID, "device chunk must be 16-byte aligned");
-  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
   Slot *s = &h->resident;
   s->text = static_cast<const uint8_t *>(d_text);
   s->nbytes = nbytes;
@@ -504,7 +525,8 @@ int b200p_parse_device_async(b200p_handle h, const void *d_text, uint64_t nbytes
 int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out) {
   if (h == NULL || out == NULL) return B200P_E_INVALID;
   if (!h->resident_pending) return Fail(h, B200P_E_EMPTY, "b200p_parse_device_finish without a pending chunk");
-  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
   h->resident_pending = false;
   const int rc = FinishParse(h, &h->resident);
   if (rc != B200P_OK) return rc;
@@ -521,7 +543,8 @@ int b200p_parse_device(b200p_handle h, const void *d_text, uint64_t nbytes, b200
 int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t nbytes) {
   if (h == NULL || (nbytes != 0 && (host_dst == NULL || device_src == NULL))) return B200P_E_INVALID;
   if (nbytes == 0) return B200P_OK;
-  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
   CUDA_TRY(h, cudaMemcpyAsync(host_dst, device_src, nbytes, cudaMemcpyDeviceToHost, h->resident.stream));
   CUDA_TRY(h, cudaStreamSynchronize(h->resident.stream));
   return B200P_OK;
@@ -566,7 +589,8 @@ static int PrepareSlot(b200p_handle h, int id, uint64_t nbytes) {
 
 int b200p_input_buffer(b200p_handle h, void **host_ptr, uint64_t *capacity) {
   if (h == NULL || host_ptr == NULL) return B200P_E_INVALID;
-  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
   if (h->lent_slot < 0) {
     const int id = FreeSlotIndex(h);
     if (id < 0) return Fail(h, B200P_E_AGAIN, "all pipeline slots are in flight: call b200p_next");
@@ -582,7 +606,8 @@ int b200p_input_buffer(b200p_handle h, void **host_ptr, uint64_t *capacity) {
 int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes) {
   if (h == NULL || (text == NULL && nbytes != 0)) return B200P_E_INVALID;
   if (nbytes > B200P_MAX_CHUNK_BYTES) return Fail(h, B200P_E_INVALID, "chunk larger than B200P_MAX_CHUNK_BYTES");
-  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
   int id = h->lent_slot;
   const bool in_place = id >= 0 && text == h->slots[id].h_text;
   if (id < 0) {
@@ -629,7 +654,8 @@ int b200p_pending(b200p_handle h) { return h != NULL ? static_cast<int>(h->in_fl
 int b200p_next(b200p_handle h, b200p_rowblock *out) {
   if (h == NULL || out == NULL) return B200P_E_INVALID;
   if (h->in_flight.empty()) return Fail(h, B200P_E_EMPTY, "b200p_next: nothing submitted");
-  CUDA_TRY(h, cudaSetDevice(h->cfg.device));
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
   const int id = h->in_flight.front();
   h->in_flight.pop_front();
   Slot *s = &h->slots[id];
@@ -787,7 +813,8 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
     }                                                                                         \
   } while (0)
 
-  NOALLOC_TRY(cudaSetDevice(rq->device));
+  DeviceScope on_device(rq->device);
+  NOALLOC_TRY(on_device.status());
   NoAllocScratch *scratch = NULL;
   NOALLOC_TRY(NoAllocScratchFor(rq->device, &scratch));
   cudaStream_t stream = static_cast<cudaStream_t>(rq->stream);
