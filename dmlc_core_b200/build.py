@@ -9,6 +9,7 @@ Targets
   gen     dmlc_core_b200/lib/libb200gen.so        synthetic-corpus generators (gcc)
   emul    tests/_build/libstrtonum_emul.so        host build of strtonum_device.h (test only)
   oracle  oracle/_build/liboracle.so (+ oracle/_ref when /root/reference is present)
+  driver  tests/_build/libsvm_parser_driver (the reference-style C++ throughput driver)
 """
 import os
 import shutil
@@ -105,6 +106,27 @@ def build_emul(force=False):
     return target
 
 
+def build_driver(force=False):
+    """tests/cpp/libsvm_parser_driver.cc against this package's headers (and, where /root/reference
+    exists, the same source against the reference's headers + oracle/_ref for comparison)."""
+    out_dir = os.path.join(ROOT, "tests", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    src = os.path.join(ROOT, "tests", "cpp", "libsvm_parser_driver.cc")
+    target = os.path.join(out_dir, "libsvm_parser_driver")
+    host = os.path.join(LIB, "libdmlc_b200_host.so")
+    if os.path.exists(host) and (force or _stale(target, [src, host])):
+        _run(["g++", "-std=c++14", "-O2", "-I" + os.path.join(PKG, "include"), src, "-L" + LIB,
+              "-ldmlc_b200_host", "-ldmlc_b200", "-Wl,-rpath,$ORIGIN/../../dmlc_core_b200/lib",
+              "-o", target])
+    ref = os.path.join(ROOT, "oracle", "_ref", "libdmlc_ref.so")
+    target_ref = os.path.join(out_dir, "libsvm_parser_driver_ref")
+    if os.path.isdir("/root/reference/include") and os.path.exists(ref) and \
+            (force or _stale(target_ref, [src, ref])):
+        _run(["g++", "-std=c++11", "-O2", "-fopenmp", "-I/root/reference/include", src, ref,
+              "-Wl,-rpath,$ORIGIN/../../oracle/_ref", "-o", target_ref])
+    return target
+
+
 def build_oracle(force=False):
     odir = os.path.join(ROOT, "oracle")
     _run(["make", "-s", "-C", odir, "oracle"])
@@ -121,11 +143,11 @@ def build_oracle(force=False):
 
 
 TARGETS = {"cuda": build_cuda, "host": build_host, "gen": build_gen, "emul": build_emul,
-           "oracle": build_oracle}
+           "oracle": build_oracle, "driver": build_driver}
 
 
 def build_all(force=False):
-    for name in ("cuda", "gen", "host", "emul", "oracle"):
+    for name in ("cuda", "gen", "host", "emul", "oracle", "driver"):
         TARGETS[name](force)
 
 
