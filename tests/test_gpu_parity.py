@@ -197,28 +197,59 @@ def test_errors_are_reported_like_the_reference(cuda_lib):
         p.close()
 
 
-def test_full_size_properties(cuda_lib, oracle):
-    """Size-independent checks at the bench's chunk size (1 GiB of dense CSV, device-resident):
-    tiling a block k times must give k copies of that block's rows (offsets shifted by nnz)."""
+@pytest.mark.parametrize("kind,fmt,ib,lc", [("csv", "csv", 4, 0), ("libsvm", "libsvm", 4, -1),
+                                            ("libfm", "libfm", 8, -1), ("libsvm_qid", "libsvm", 4, -1)])
+def test_full_size_properties(cuda_lib, oracle, kind, fmt, ib, lc):
+    """Size-independent checks at the largest chunk the ABI takes (1 GiB, device-resident):
+    tiling a block k times must give k copies of that block's rows, offsets shifted by the block's
+    nnz; and the first copy is the oracle's answer on one block."""
     import torch
     from dmlc_core_b200 import datagen
     from gpu_util import as_torch
-    base, rows = datagen.generate("csv", 1, 32 << 20)
+    base, rows = datagen.generate(kind, 1, 32 << 20)
+    pad = (-base.size) % 16
+    base = np.concatenate([base, np.full(pad, 10, dtype=np.uint8)])   # blank lines are skipped
+    small = oracle.parse_buffer(fmt, base.tobytes(), ib, lc)
+    nnz1 = len(small["index"])
     k = (1 << 30) // base.size
     big = torch.from_numpy(base).cuda().repeat(k)
-    p = _parser(cuda_lib, "csv", 4, 0)
+    p = _parser(cuda_lib, fmt, ib, lc)
     blk = p.parse_device(big.data_ptr(), big.numel())
-    assert blk.rows == rows * k and blk.nnz == rows * k * 128 and blk.n_value == blk.nnz
-    value = as_torch(blk.value, blk.nnz, np.float32).view(k, -1)
-    index = as_torch(blk.index, blk.nnz, np.uint32).view(k, -1)
-    label = as_torch(blk.label, blk.rows, np.float32).view(k, -1)
-    offset = as_torch(blk.offset, blk.rows + 1, np.uint64)
-    assert bool((value == value[0:1]).all()) and bool((index == index[0:1]).all())
-    assert bool((label == label[0:1]).all())
-    assert bool((offset == torch.arange(blk.rows + 1, device="cuda", dtype=torch.int64) * 128).all())
-    # and the first copy is the oracle's answer on one block
-    small = oracle.parse_buffer("csv", base.tobytes(), 4, 0)
-    assert np.array_equal(value[0].cpu().numpy().view(np.uint32), small["value"].view(np.uint32))
+    assert blk.rows == rows * k and blk.nnz == nnz1 * k
+    assert blk.n_value == len(small["value"]) * k and blk.n_weight == len(small["weight"]) * k
+    assert blk.n_qid == len(small["qid"]) * k and blk.n_field == len(small["field"]) * k
+    idt = np.uint64 if ib == 8 else np.uint32
+
+    def copies(ptr, n, dt):
+        return as_torch(ptr, n, dt).view(k, -1)
+    index = copies(blk.index, blk.nnz, idt)
+    label = copies(blk.label, blk.rows, np.float32)
+    assert bool((index == index[0:1]).all()) and bool((label == label[0:1]).all())
+    assert np.array_equal(index[0].cpu().numpy().view(idt), small["index"])
     assert np.array_equal(label[0].cpu().numpy().view(np.uint32), small["label"].view(np.uint32))
-    assert np.array_equal(index[0].cpu().numpy().view(np.uint32), small["index"])
+    for name, ptr, n, dt in (("value", blk.value, blk.n_value, np.float32), ("weight", blk.weight, blk.n_weight, np.float32),
+                             ("qid", blk.qid, blk.n_qid, np.uint64), ("field", blk.field, blk.n_field, idt)):
+        if n:
+            t = copies(ptr, n, dt)
+            assert bool((t == t[0:1]).all()), name
+            got = t[0].cpu().numpy()
+            want = small[name]
+            assert np.array_equal(got.view(np.uint32) if dt == np.float32 else got.view(dt), 
+                                  want.view(np.uint32) if dt == np.float32 else want), name
+    offset = as_torch(blk.offset, blk.rows + 1, np.uint64)
+    body = offset[:-1].view(k, -1)
+    shift = torch.arange(k, device="cuda", dtype=torch.int64).view(k, 1) * nnz1
+    assert bool((body - shift == body[0:1]).all()) and int(offset[-1].item()) == nnz1 * k
+    assert np.array_equal(body[0].cpu().numpy().view(np.uint64), small["offset"][:-1])
+    assert blk.max_index == int(small["index"].max())
+    p.close()
+
+
+def test_oversize_chunk_is_refused(cuda_lib):
+    from dmlc_core_b200 import capi
+    p = _parser(cuda_lib, "libsvm")
+    with pytest.raises(RuntimeError, match="B200P_MAX_CHUNK_BYTES"):
+        p.parse_device_async(256, capi.MAX_CHUNK_BYTES + 1)     # refused before anything is touched
+    with pytest.raises(RuntimeError, match="16-byte aligned"):
+        p.parse_device_async(257, 64)
     p.close()
