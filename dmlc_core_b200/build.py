@@ -5,6 +5,7 @@
 
 Targets
   cuda    dmlc_core_b200/lib/libdmlc_b200.so      the C ABI + sm_100a kernels (nvcc)
+  checked dmlc_core_b200/lib/libdmlc_b200_checked.so  same, bounds-checked (-DB200P_CHECKED, tests)
   host    dmlc_core_b200/lib/libdmlc_b200_host.so the dmlc::Parser<IndexType> C++ layer (g++)
   gen     dmlc_core_b200/lib/libb200gen.so        synthetic-corpus generators (gcc)
   emul    tests/_build/libstrtonum_emul.so        host build of strtonum_device.h (test only)
@@ -61,6 +62,19 @@ def build_cuda(force=False):
     if force or _stale(target, srcs):
         _run([_nvcc()] + NVCC_ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
                                       "-shared", "--cudart", "static", "-o", target,
+                                      os.path.join(PKG, "csrc", "b200_parser.cu")])
+    return target
+
+
+def build_cuda_checked(force=False):
+    """The same library with -DB200P_CHECKED: bounds-checked queues and stores (test build)."""
+    os.makedirs(LIB, exist_ok=True)
+    target = os.path.join(LIB, "libdmlc_b200_checked.so")
+    srcs = _glob(os.path.join(PKG, "csrc"), (".cu", ".cuh", ".h")) + \
+        [os.path.join(ROOT, "include", "dmlc_b200_parser.h")]
+    if force or _stale(target, srcs):
+        _run([_nvcc()] + NVCC_ARCH + ["-lineinfo", "-O3", "-std=c++17", "-DB200P_CHECKED", "-Xcompiler",
+                                      "-fPIC", "-shared", "--cudart", "static", "-o", target,
                                       os.path.join(PKG, "csrc", "b200_parser.cu")])
     return target
 
@@ -143,11 +157,11 @@ def build_oracle(force=False):
 
 
 TARGETS = {"cuda": build_cuda, "host": build_host, "gen": build_gen, "emul": build_emul,
-           "oracle": build_oracle, "driver": build_driver}
+           "oracle": build_oracle, "driver": build_driver, "checked": build_cuda_checked}
 
 
 def build_all(force=False):
-    for name in ("cuda", "gen", "host", "emul", "oracle", "driver"):
+    for name in ("cuda", "checked", "gen", "host", "emul", "oracle", "driver"):
         TARGETS[name](force)
 
 

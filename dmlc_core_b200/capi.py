@@ -10,7 +10,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libdmlc_b200.so")
+# DMLC_B200_LIB selects another build of the same library (the bounds-checked test build)
+LIB_PATH = os.environ.get("DMLC_B200_LIB") or os.path.join(_HERE, "lib", "libdmlc_b200.so")
 
 LIBSVM, LIBFM, CSV = 0, 1, 2
 FORMATS = {"libsvm": LIBSVM, "libfm": LIBFM, "csv": CSV}

@@ -351,6 +351,9 @@ static int FinishParse(b200p_handle h, Slot *s) {
   }
   h->rows_per_byte = std::max(h->rows_per_byte, static_cast<double>(sum.total[kRows]) / s->nbytes);
   h->nnz_per_byte = std::max(h->nnz_per_byte, static_cast<double>(sum.total[kNnz]) / s->nbytes);
+  if (sum.error & kErrInternal) {
+    return Fail(h, B200P_E_CUDA, "internal consistency check failed (checked build): a queue or output index left its bounds");
+  }
   if (sum.error & kErrNegativeIndex) {
     return Fail(h, B200P_E_PARSE, "Check failed: sign == true (negative value in an unsigned index/field)");
   }
@@ -417,7 +420,11 @@ static int InitSlot(b200p_handle h, Slot *s, cudaStream_t stream) {
 /* ------------------------------------------------------------------ C ABI ------------------- */
 extern "C" {
 
+#ifdef B200P_CHECKED
+const char *b200p_version(void) { return "dmlc_b200 0.1 sm_100a checked"; }
+#else
 const char *b200p_version(void) { return "dmlc_b200 0.1 sm_100a"; }
+#endif
 
 const char *b200p_last_error(b200p_handle h) {
   return h != NULL ? h->error.c_str() : g_create_error.c_str();

@@ -49,7 +49,22 @@ enum ErrorBits {
   kErrNegativeIndex = 1u,   /* reference strtonum.h:141  CHECK_EQ(sign, true) */
   kErrValueCount = 2u,      /* reference row_block.h:177 offset.back()==value.size()||empty */
   kErrCapacity = 4u,        /* output buffers too small: host grows them and re-runs pass 2 */
+  kErrInternal = 8u,        /* checked build only: a queue or output index left its bounds */
 };
+
+/*
+ * Checked build (-DB200P_CHECKED, libdmlc_b200_checked.so): every shared-memory queue write and
+ * every store into a CSR array is bounds-checked against the queue size / the totals pass 1
+ * counted; a violation sets kErrInternal instead of writing.  compute-sanitizer is not available
+ * on the GPU pool, so the GPU tests run a corpus + fuzz subset through this build instead
+ * (tests/test_gpu_checked_build.py).  The production build compiles the checks away.
+ */
+#ifdef B200P_CHECKED
+#define B200P_CHECK(prm, cond) \
+  if (!(cond)) { atomicOr(&(prm).summary->error, static_cast<unsigned int>(kErrInternal)); } else
+#else
+#define B200P_CHECK(prm, cond)
+#endif
 
 constexpr int kStepBytes = 512;        /* one warp step: 32 lanes x 16 B */
 constexpr int kWarpsPerCta = 8;
@@ -309,20 +324,29 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
   const uint32_t need = flush ? 1u : 32u;
   while (st.n_label >= need) {
     const uint32_t take = min(st.n_label, 32u);
-    if (lane < take) prm.label[st.w_label + lane] = ToFloatFast(txt, ws.q_label[lane]);
+    if (lane < take) {
+      B200P_CHECK(prm, st.w_label + lane < prm.summary->total[kRows])
+      prm.label[st.w_label + lane] = ToFloatFast(txt, ws.q_label[lane]);
+    }
     st.w_label += take;
     QueuePop(ws.q_label, st.n_label, take, lane);
   }
   while (st.n_weight >= need) {
     const uint32_t take = min(st.n_weight, 32u);
-    if (lane < take) prm.weight[st.w_weight + lane] = ToFloatFast(txt, ws.q_weight[lane]);
+    if (lane < take) {
+      B200P_CHECK(prm, st.w_weight + lane < prm.summary->total[kWeights])
+      prm.weight[st.w_weight + lane] = ToFloatFast(txt, ws.q_weight[lane]);
+    }
     st.w_weight += take;
     QueuePop(ws.q_weight, st.n_weight, take, lane);
   }
   if (FMT == kLibSVM) {
     while (st.n_qid >= need) {
       const uint32_t take = min(st.n_qid, 32u);
-      if (lane < take) prm.qid[st.w_qid + lane] = ToQid(txt, ws.q_qid[lane]);
+      if (lane < take) {
+        B200P_CHECK(prm, st.w_qid + lane < prm.summary->total[kQids])
+        prm.qid[st.w_qid + lane] = ToQid(txt, ws.q_qid[lane]);
+      }
       st.w_qid += take;
       QueuePop(ws.q_qid, st.n_qid, take, lane);
     }
@@ -332,10 +356,12 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
     bool neg = false;
     if (lane < take) {
       const unsigned long long idx = ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg);
+      B200P_CHECK(prm, st.w_index + lane < prm.summary->total[kNnz])
       StoreIdx<IdxT>(prm.index, st.w_index + lane, idx);
       st.max_index = max(st.max_index, idx);
       if (FMT == kLibFM) {
         const unsigned long long fld = ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg);
+        B200P_CHECK(prm, st.w_index + lane < prm.summary->total[kNnz])
         StoreIdx<IdxT>(prm.field, st.w_index + lane, fld);
         st.max_field = max(st.max_field, fld);
       }
@@ -350,7 +376,10 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
   }
   while (st.n_value >= need) {
     const uint32_t take = min(st.n_value, 32u);
-    if (lane < take) prm.value[st.w_value + lane] = ToFloatFast(txt, ws.q_value[lane]);
+    if (lane < take) {
+      B200P_CHECK(prm, st.w_value + lane < prm.summary->total[kValues])
+      prm.value[st.w_value + lane] = ToFloatFast(txt, ws.q_value[lane]);
+    }
     st.w_value += take;
     QueuePop(ws.q_value, st.n_value, take, lane);
   }
@@ -498,6 +527,7 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
     /* row pointer: a label token opens row r; offset[r] = features stored before it
        (libsvm_parser.h:62-64 push the running index count) */
     if (is_label) {
+      B200P_CHECK(prm, st.seen[kRows] + __popc(m_label & lt) < prm.summary->total[kRows])
       prm.offset[st.seen[kRows] + __popc(m_label & lt)] =
           static_cast<unsigned long long>(st.seen[kNnz] + __popc(m_index & lt));
     }
@@ -506,15 +536,27 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
          (libfm_parser.h:73), so a '-' raises even on a token that is then dropped */
       st.error |= kErrNegativeIndex;
     }
-    if (is_label) ws.q_label[st.n_label + __popc(m_label & lt)] = at;
-    if (is_weight) ws.q_weight[st.n_weight + __popc(m_weight & lt)] = at;
+    if (is_label) {
+      B200P_CHECK(prm, st.n_label + __popc(m_label & lt) < kRoleQueue)
+      ws.q_label[st.n_label + __popc(m_label & lt)] = at;
+    }
+    if (is_weight) {
+      B200P_CHECK(prm, st.n_weight + __popc(m_weight & lt) < kRoleQueue)
+      ws.q_weight[st.n_weight + __popc(m_weight & lt)] = at;
+    }
     if (is_index) {
       const uint32_t slot = st.n_index + __popc(m_index & lt);
-      ws.q_index[slot] = at;
-      if (FMT == kLibFM) ws.q_field[slot] = prev_at;
+      B200P_CHECK(prm, slot < kRoleQueue) {
+        ws.q_index[slot] = at;
+        if (FMT == kLibFM) ws.q_field[slot] = prev_at;
+      }
     }
-    if (is_value) ws.q_value[st.n_value + __popc(m_value & lt)] = at;
+    if (is_value) {
+      B200P_CHECK(prm, st.n_value + __popc(m_value & lt) < kRoleQueue)
+      ws.q_value[st.n_value + __popc(m_value & lt)] = at;
+    }
     if (FMT == kLibSVM && is_qid) {
+      B200P_CHECK(prm, st.n_qid + __popc(m_qid & lt) < kRoleQueue)
       ws.q_qid[st.n_qid + __popc(m_qid & lt)] = (prev_pos == 1) ? qid_at_a : qid_at_b;
     }
     st.n_label += __popc(m_label);
@@ -567,19 +609,23 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
   if (EMIT) {
     const uint32_t row = st.seen[kRows] + __popc(rs_m & LaneMaskLe()) - 1u; /* row of this field */
     if (row_start) {
+      B200P_CHECK(prm, st.seen[kRows] + __popc(rs_m & lt) < prm.summary->total[kRows])
       prm.offset[st.seen[kRows] + __popc(rs_m & lt)] =
           static_cast<unsigned long long>(st.seen[kNnz] + __popc(m_value & lt));
     }
     if (active) {
       const float v = ToFloatFast(txt, at);
       if (is_label) {
+        B200P_CHECK(prm, row < prm.summary->total[kRows])
         prm.label[row] = v;
       } else {
         const uint32_t slot = st.seen[kNnz] + __popc(m_value & lt);
         const uint32_t idx =
             col - ((prm.label_column >= 0 && static_cast<int32_t>(col) > prm.label_column) ? 1u : 0u);
-        prm.value[slot] = v;
-        StoreIdx<IdxT>(prm.index, slot, idx);
+        B200P_CHECK(prm, slot < prm.summary->total[kNnz]) {
+          prm.value[slot] = v;
+          StoreIdx<IdxT>(prm.index, slot, idx);
+        }
         st.max_index = max(st.max_index, static_cast<unsigned long long>(idx));
       }
     }
@@ -715,7 +761,9 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
         while (bits != 0u) {
           const uint32_t b = __ffs(bits) - 1;     /* 2 * byte offset */
           bits &= bits - 1u;
-          ws.tokens[slot++] = first2 + b + ((row_starts >> b) & 1u);
+          B200P_CHECK(prm, slot < kFieldQueue)
+          ws.tokens[slot] = first2 + b + ((row_starts >> b) & 1u);
+          ++slot;
         }
         fill += __shfl_sync(0xffffffffu, incl, 31);
         __syncwarp();
@@ -767,13 +815,17 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
         while (bits != 0u) {
           const uint32_t b = __ffs(bits) - 1;     /* 4 * byte offset */
           bits &= bits - 1u;
-          ws.tokens[slot++] = first4 + b + SeparatorKind(__funnelshift_r(p_lo, p_mid, b) & 0xffu);
+          B200P_CHECK(prm, slot < kTokenQueue)
+          ws.tokens[slot] = first4 + b + SeparatorKind(__funnelshift_r(p_lo, p_mid, b) & 0xffu);
+          ++slot;
         }
         bits = s1;
         while (bits != 0u) {
           const uint32_t b = __ffs(bits) - 1;
           bits &= bits - 1u;
-          ws.tokens[slot++] = first4 + 32u + b + SeparatorKind(__funnelshift_r(p_mid, p_hi, b) & 0xffu);
+          B200P_CHECK(prm, slot < kTokenQueue)
+          ws.tokens[slot] = first4 + 32u + b + SeparatorKind(__funnelshift_r(p_mid, p_hi, b) & 0xffu);
+          ++slot;
         }
         fill += __shfl_sync(0xffffffffu, incl, 31);
         __syncwarp();
@@ -812,6 +864,27 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
     }
   }
 
+#ifdef B200P_CHECKED
+  if (EMIT) {
+    /* pass 2 must have produced exactly what pass 1 counted for this range */
+    bool same = true;
+#pragma unroll
+    for (int c = 0; c < kNumCounters; ++c) {
+      const unsigned long long next =
+          range + 1 < prm.num_ranges
+              ? static_cast<unsigned long long>(prm.counts[c * prm.num_ranges + range + 1]) +
+                    prm.tile_base[c * prm.num_tiles + (range + 1) / kScanTile]
+              : prm.summary->total[c];
+      same = same && (static_cast<unsigned long long>(st.seen[c]) == next);
+    }
+    if (FMT != kCSV) { /* the role queues must have drained to the same positions */
+      same = same && st.w_label == st.seen[kRows] && st.w_index == st.seen[kNnz] &&
+             st.w_value == st.seen[kValues] && st.w_weight == st.seen[kWeights] &&
+             st.w_qid == st.seen[kQids];
+    }
+    if (!same) st.error |= kErrInternal;
+  }
+#endif
   if (EMIT) {
     const uint32_t err = __reduce_or_sync(0xffffffffu, st.error);
     if (err != 0u && lane == 0) atomicOr(&prm.summary->error, err);
