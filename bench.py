@@ -86,7 +86,7 @@ class ClockSampler(object):
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
@@ -239,6 +239,9 @@ def main():
         raise SystemExit("bench.py needs a GPU (there is no CPU path)")
     torch.cuda.set_device(local)
     if world > 1:
+        # NCCL_DEBUG=VERSION (set on some boxes) makes NCCL print a banner on stdout, which must
+        # carry exactly one JSON line
+        os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -279,22 +282,31 @@ def main():
         return blk
 
     # ---------------- device-resident: value --------------------------------------------------
+    # clocks are sampled from the warm-up on: the timed region itself (tens of ms) is shorter than
+    # nvidia-smi's polling period, and the warm-up runs the very same kernels back to back
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(max(args.warmup, 3)):
         blk = device_step()
     rows = int(blk.rows)
     nnz = int(blk.nnz)
     assert rows == rows_block and nnz == rows * CSV_COLS, (rows, rows_block, nnz)
     launches0 = p.launch_count()
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     for _ in range(args.steps):
         device_step()
     ev1.record(stream)
     barrier()
+    # the timed region lasts tens of ms; keep the identical load running (untimed) until
+    # nvidia-smi has delivered a few samples
+    t_extra = time.time()
+    while len(sampler.lines) < 4 and time.time() - t_extra < 3.0:
+        device_step()
+    torch.cuda.synchronize()
     clocks = sampler.stop()
+    clocks["window"] = "warm-up + timed steps + identical untimed steps until >= 4 samples"
     dev_ms = max_over_ranks(ev0.elapsed_time(ev1)) / args.steps
     launches = p.launch_count() - launches0
     value = world * text_bytes / (dev_ms * 1e-3) / GB
