@@ -25,6 +25,7 @@ EXPORTS = (
     "b200p_parse_device_async", "b200p_parse_device_finish", "b200p_input_buffer",
     "b200p_submit", "b200p_next", "b200p_pending", "b200p_fetch", "b200p_launch_count",
     "b200p_set_profiling", "b200p_kernel_time", "b200p_version", "b200p_parse_device_noalloc",
+    "b200p_block_max",
 )
 
 
@@ -44,7 +45,7 @@ class RowBlock(C.Structure):
                 ("offset", C.c_void_p), ("label", C.c_void_p), ("weight", C.c_void_p),
                 ("qid", C.c_void_p), ("field", C.c_void_p), ("index", C.c_void_p),
                 ("value", C.c_void_p), ("text_bytes", C.c_uint64), ("index_bytes", C.c_int32),
-                ("on_device", C.c_int32), ("max_index", C.c_uint64), ("max_field", C.c_uint64)]
+                ("on_device", C.c_int32)]
 
 
 class NoAllocRequest(C.Structure):
@@ -91,6 +92,8 @@ def load():
     lib.b200p_pending.restype = C.c_int
     lib.b200p_fetch.argtypes = [H, C.c_void_p, C.c_void_p, C.c_uint64]
     lib.b200p_fetch.restype = C.c_int
+    lib.b200p_block_max.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.b200p_block_max.restype = C.c_int
     lib.b200p_launch_count.argtypes = [H]
     lib.b200p_launch_count.restype = C.c_uint64
     lib.b200p_set_profiling.argtypes = [H, C.c_int]
@@ -231,6 +234,12 @@ class Parser(object):
             "value": _host_array(blk.value, blk.n_value, np.float32),
             "error": 0,
         }
+
+    def block_max(self):
+        """(max index, max field) of the block returned last, reduced on the GPU."""
+        mi, mf = C.c_uint64(0), C.c_uint64(0)
+        self._check(self.lib.b200p_block_max(self.handle, C.byref(mi), C.byref(mf)))
+        return int(mi.value), int(mf.value)
 
     def pending(self):
         return int(self.lib.b200p_pending(self.handle))

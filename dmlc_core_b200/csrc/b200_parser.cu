@@ -76,8 +76,10 @@ struct b200p_parser_s {
   std::deque<int> in_flight; /* slot ids, oldest first */
   int lent_slot;             /* slot whose pinned input buffer was handed out, or -1 */
   int returned_slot;         /* slot whose host arrays the caller currently holds, or -1 */
+  const Slot *last_block;    /* slot whose device arrays hold the block handed out last */
   double rows_per_byte, nnz_per_byte; /* densest chunk seen so far: sizes later allocations */
   uint64_t launches;
+  unsigned long long *d_max; /* two words for b200p_block_max, allocated on first use */
   /* optional per-kernel timing (b200p_set_profiling): event pairs around each launch */
   bool profiling;
   struct Timed { int kind; cudaEvent_t start, stop; };
@@ -378,8 +380,6 @@ static void FillBlock(const b200p_handle h, const Slot &s, const Arrays &a, bool
   out->n_qid = sum.total[kQids];
   out->n_value = sum.total[kValues];
   out->n_field = h->cfg.format == B200P_FORMAT_LIBFM ? out->nnz : 0;
-  out->max_index = sum.max_index;
-  out->max_field = sum.max_field;
   if (out->rows == 0) return;
   out->offset = reinterpret_cast<const uint64_t *>(a.offset);
   out->label = a.label;
@@ -450,9 +450,11 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->depth = config->depth > 0 ? std::min(config->depth, 8) : 3;
   h->lent_slot = -1;
   h->returned_slot = -1;
+  h->last_block = NULL;
   h->resident_pending = false;
   h->rows_per_byte = h->nnz_per_byte = 0.0;
   h->launches = 0;
+  h->d_max = NULL;
   h->profiling = false;
   for (int k = 0; k < 3; ++k) { h->kernel_ms[k] = 0.0; h->kernel_launches[k] = 0; }
 
@@ -492,6 +494,7 @@ void b200p_destroy(b200p_handle h) {
   ProfCollect(h);
   for (size_t i = 0; i < h->slots.size(); ++i) DestroySlot(&h->slots[i]);
   DestroySlot(&h->resident);
+  cudaFree(h->d_max);
   delete h;
 }
 
@@ -538,6 +541,7 @@ int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out) {
   const int rc = FinishParse(h, &h->resident);
   if (rc != B200P_OK) return rc;
   FillBlock(h, h->resident, h->resident.dev, true, out);
+  h->last_block = &h->resident;
   return B200P_OK;
 }
 
@@ -545,6 +549,41 @@ int b200p_parse_device(b200p_handle h, const void *d_text, uint64_t nbytes, b200
   const int rc = b200p_parse_device_async(h, d_text, nbytes);
   if (rc != B200P_OK) return rc;
   return b200p_parse_device_finish(h, out);
+}
+
+int b200p_block_max(b200p_handle h, uint64_t *max_index, uint64_t *max_field) {
+  if (h == NULL) return B200P_E_INVALID;
+  if (max_index != NULL) *max_index = 0;
+  if (max_field != NULL) *max_field = 0;
+  if (h->last_block == NULL) return Fail(h, B200P_E_EMPTY, "b200p_block_max: no block has been returned yet");
+  const Slot *s = h->last_block;
+  if (s->nbytes == 0) return B200P_OK;
+  const uint64_t nnz = s->h_summary->total[kNnz];
+  if (nnz == 0) return B200P_OK;
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
+  /* two result words of its own, allocated once */
+  if (h->d_max == NULL) CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&h->d_max), 2 * sizeof(unsigned long long)));
+  CUDA_TRY(h, cudaMemsetAsync(h->d_max, 0, 2 * sizeof(unsigned long long), s->stream));
+  const unsigned grid = static_cast<unsigned>(std::min<uint64_t>((nnz + 255) / 256, 148 * 8));
+  const bool wide = h->cfg.index_bytes == 8;
+  if (wide) {
+    MaxOfArray<uint64_t><<<grid, 256, 0, s->stream>>>(static_cast<const uint64_t *>(s->dev.index), nnz, h->d_max);
+    if (h->cfg.format == B200P_FORMAT_LIBFM)
+      MaxOfArray<uint64_t><<<grid, 256, 0, s->stream>>>(static_cast<const uint64_t *>(s->dev.field), nnz, h->d_max + 1);
+  } else {
+    MaxOfArray<uint32_t><<<grid, 256, 0, s->stream>>>(static_cast<const uint32_t *>(s->dev.index), nnz, h->d_max);
+    if (h->cfg.format == B200P_FORMAT_LIBFM)
+      MaxOfArray<uint32_t><<<grid, 256, 0, s->stream>>>(static_cast<const uint32_t *>(s->dev.field), nnz, h->d_max + 1);
+  }
+  h->launches += h->cfg.format == B200P_FORMAT_LIBFM ? 2 : 1;
+  CUDA_TRY(h, cudaGetLastError());
+  unsigned long long host[2] = {0ull, 0ull};
+  CUDA_TRY(h, cudaMemcpyAsync(host, h->d_max, sizeof(host), cudaMemcpyDeviceToHost, s->stream));
+  CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+  if (max_index != NULL) *max_index = host[0];
+  if (max_field != NULL) *max_field = host[1];
+  return B200P_OK;
 }
 
 int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t nbytes) {
@@ -668,6 +707,7 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
   Slot *s = &h->slots[id];
   s->busy = false;
   h->returned_slot = -1; /* the block handed out before this call is released now */
+  h->last_block = NULL;
   int rc = FinishParse(h, s);
   if (rc != B200P_OK) return rc;
   if (s->nbytes != 0) {
@@ -692,6 +732,7 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
   }
   FillBlock(h, *s, s->host, false, out);
   h->returned_slot = id;
+  h->last_block = s;
   return B200P_OK;
 }
 
@@ -872,8 +913,6 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
   out->n_qid = sum.total[kQids];
   out->n_value = sum.total[kValues];
   out->n_field = need_field ? out->nnz : 0;
-  out->max_index = sum.max_index;
-  out->max_field = sum.max_field;
   if (sum.total[kRows] > rq->cap_rows || sum.total[kNnz] > rq->cap_nnz) {
     /* pass 2 wrote nothing; rows / nnz tell the caller how much room this chunk needs */
     if (errbuf != NULL && errlen != 0) {

@@ -77,8 +77,6 @@ constexpr int kRoleQueue = 64;         /* < 32 left over + <= 32 new per token g
 /* Result header written by ScanFinish (device memory, copied to the host per chunk). */
 struct ChunkSummary {
   unsigned long long total[kNumCounters];
-  unsigned long long max_index;  /* largest feature index / field id stored by pass 2: what */
-  unsigned long long max_field;  /* RowBlockContainer::Push tracks on the CPU (row_block.h:143,153) */
   unsigned int error;
   unsigned int ranges;
 };
@@ -284,7 +282,8 @@ struct WarpScratch {
   uint32_t q_value[FMT == kCSV ? 1 : kRoleQueue];
 };
 
-/* State of one warp while it walks its range. All members are warp-uniform. */
+/* State of one warp while it walks its range. All members are warp-uniform except error. */
+template <typename IdxT>
 struct WalkState {
   uint32_t seen[kNumCounters];  /* pass 1: counts so far; pass 2: absolute output cursors for
                                    the *role pass* (offset/label row ids, nnz ids) */
@@ -297,9 +296,12 @@ struct WalkState {
   uint32_t n_label, n_weight, n_qid, n_index, n_value;
   uint32_t w_label, w_weight, w_qid, w_index, w_value;
   uint32_t error;
-  unsigned long long max_index, max_field; /* per lane; reduced when the walk ends */
 };
 
+template <typename T>
+__device__ __forceinline__ T MaxOf(T a, T b) {
+  return a > b ? a : b;
+}
 template <typename IdxT>
 __device__ __forceinline__ void StoreIdx(void *base, uint32_t at, uint64_t v) {
   reinterpret_cast<IdxT *>(base)[at] = static_cast<IdxT>(v);
@@ -319,7 +321,7 @@ __device__ __forceinline__ void QueuePop(uint32_t *q, uint32_t &fill, uint32_t t
 
 template <int FMT, typename IdxT>
 __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Text &txt,
-                                                WarpScratch<FMT> &ws, WalkState &st, int lane,
+                                                WarpScratch<FMT> &ws, WalkState<IdxT> &st, int lane,
                                                 bool flush) {
   const uint32_t need = flush ? 1u : 32u;
   while (st.n_label >= need) {
@@ -355,15 +357,13 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
     const uint32_t take = min(st.n_index, 32u);
     bool neg = false;
     if (lane < take) {
-      const unsigned long long idx = ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg);
-      B200P_CHECK(prm, st.w_index + lane < prm.summary->total[kNnz])
-      StoreIdx<IdxT>(prm.index, st.w_index + lane, idx);
-      st.max_index = max(st.max_index, idx);
-      if (FMT == kLibFM) {
-        const unsigned long long fld = ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg);
-        B200P_CHECK(prm, st.w_index + lane < prm.summary->total[kNnz])
-        StoreIdx<IdxT>(prm.field, st.w_index + lane, fld);
-        st.max_field = max(st.max_field, fld);
+      B200P_CHECK(prm, st.w_index + lane < prm.summary->total[kNnz]) {
+        StoreIdx<IdxT>(prm.index, st.w_index + lane,
+                       ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_index[lane], &neg));
+        if (FMT == kLibFM) {
+          StoreIdx<IdxT>(prm.field, st.w_index + lane,
+                         ToUintFast<sizeof(IdxT) == 8>(txt, ws.q_field[lane], &neg));
+        }
       }
     }
     if (neg) st.error |= kErrNegativeIndex; /* lane-local; OR-reduced at the end of the walk */
@@ -395,7 +395,7 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
  */
 template <int FMT, typename IdxT, bool EMIT>
 __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &txt,
-                                           WarpScratch<FMT> &ws, WalkState &st, uint32_t head,
+                                           WarpScratch<FMT> &ws, WalkState<IdxT> &st, uint32_t head,
                                            uint32_t count, int lane) {
   const bool active = lane < count;
   const uint32_t entry = active ? ws.tokens[head + lane] : 3u;
@@ -408,7 +408,45 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
   bool qid_a = false, qid_b = false;     /* separator is [blank]*"qid:"... / [space]*"qid:"... */
   uint32_t qid_at_a = 0, qid_at_b = 0;   /* byte after that "qid:" */
   const bool general = active && kind == 0u;
-  if (__any_sync(0xffffffffu, general)) {
+  const uint32_t general_m = __ballot_sync(0xffffffffu, general);
+  if (!EMIT && general_m == 0u) {
+    /* Counting shortcut.  With only the three simple separator kinds in the group and no chain
+       longer than three tokens, the role counts are plain mask arithmetic on warp-uniform
+       ballots -- no per-lane chain positions.  Anything else takes the general code below,
+       which pass 2 always uses; both implement the same rules (the checked build verifies that
+       pass 2 produces exactly what pass 1 counted). */
+    const uint32_t act_m = count >= 32u ? 0xffffffffu : ((1u << count) - 1u);
+    const uint32_t line_m = __ballot_sync(0xffffffffu, active && kind == 3u);
+    const uint32_t bound_m = __ballot_sync(0xffffffffu, active && kind == 1u);
+    const uint32_t start_m = act_m & ~bound_m;                    /* chain position 1 */
+    const uint32_t c1 = st.carry_pos == 1 ? 1u : 0u, c2 = st.carry_pos == 2 ? 1u : 0u;
+    const uint32_t c3 = st.carry_pos >= 3 ? 1u : 0u, cf = st.carry_first ? 1u : 0u;
+    const uint32_t p2 = bound_m & ((start_m << 1) | c1);          /* chain position 2 */
+    const uint32_t p3 = bound_m & ((p2 << 1) | c2);               /* chain position 3 */
+    const uint32_t p4 = bound_m & ((p3 << 1) | c3);               /* longer chains */
+    if (p4 == 0u) {
+      const uint32_t p2f = p2 & ((line_m << 1) | (c1 & cf));      /* ... in the line's first chain */
+      const uint32_t p3f = p3 & ((p2f << 1) | (c2 & cf));
+      uint32_t index_m, value_m;
+      if (FMT == kLibSVM) {
+        index_m = (start_m & ~line_m) | p3;   /* first chain: label, weight, index; else index, value, index */
+        value_m = p2 & ~p2f;
+      } else {
+        index_m = p2 & ~p2f;                  /* field:index[:value]; a first-chain position 3 opens */
+        value_m = p3 & ~p3f;                  /* a triple that no index follows: dropped */
+      }
+      st.seen[kRows] += __popc(line_m);
+      st.seen[kNnz] += __popc(index_m);
+      st.seen[kValues] += __popc(value_m);
+      st.seen[kWeights] += __popc(p2f);
+      const uint32_t last = 1u << (count - 1u);
+      st.carry_pos = (p3 & last) ? 3 : ((p2 & last) ? 2 : 1);
+      st.carry_first = ((line_m | p2f | p3f) & last) != 0u;
+      st.carry_at = __shfl_sync(0xffffffffu, at, static_cast<int>(count) - 1);
+      return;
+    }
+  }
+  if (general_m != 0u) {
     /* not one of the three common separators: walk back over it */
     /* the one longer separator that well-formed ranking data has on every row,
        "<digit-run byte> qid:" (libsvm_parser.h:66-75), is recognised without the walk */
@@ -588,7 +626,7 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
  */
 template <typename IdxT, bool EMIT>
 __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &txt,
-                                           WarpScratch<kCSV> &ws, WalkState &st, uint32_t head,
+                                           WarpScratch<kCSV> &ws, WalkState<IdxT> &st, uint32_t head,
                                            uint32_t count, int lane) {
   const bool active = lane < count;
   const uint32_t entry = active ? ws.tokens[head + lane] : 0u;
@@ -626,7 +664,6 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
           prm.value[slot] = v;
           StoreIdx<IdxT>(prm.index, slot, idx);
         }
-        st.max_index = max(st.max_index, static_cast<unsigned long long>(idx));
       }
     }
   }
@@ -674,7 +711,7 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
     begin = (e == 0xffffffffu) ? hi : e + 1u;
   }
 
-  WalkState st;
+  WalkState<IdxT> st;
 #pragma unroll
   for (int c = 0; c < kNumCounters; ++c) st.seen[c] = 0;
   st.carry_pos = 0;
@@ -684,7 +721,6 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   st.n_label = st.n_weight = st.n_qid = st.n_index = st.n_value = 0;
   st.w_label = st.w_weight = st.w_qid = st.w_index = st.w_value = 0;
   st.error = 0;
-  st.max_index = st.max_field = 0;
   if (EMIT) {
 #pragma unroll
     for (int c = 0; c < kNumCounters; ++c) {
@@ -888,16 +924,6 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
   if (EMIT) {
     const uint32_t err = __reduce_or_sync(0xffffffffu, st.error);
     if (err != 0u && lane == 0) atomicOr(&prm.summary->error, err);
-    unsigned long long mi = st.max_index, mf = st.max_field;
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-      mi = max(mi, __shfl_xor_sync(0xffffffffu, mi, d));
-      mf = max(mf, __shfl_xor_sync(0xffffffffu, mf, d));
-    }
-    if (lane == 0) {
-      if (mi != 0ull) atomicMax(&prm.summary->max_index, mi);
-      if (FMT == kLibFM && mf != 0ull) atomicMax(&prm.summary->max_field, mf);
-    }
   } else {
     if (lane < kNumCounters) {
       uint32_t v = 0;
@@ -973,8 +999,29 @@ __global__ void __launch_bounds__(kScanTile) ScanFinish(uint32_t *tile_base, uin
     if (grand[kValues] != 0ull && grand[kValues] != grand[kNnz]) err |= kErrValueCount;
     summary->error = err;
     summary->ranges = num_ranges;
-    summary->max_index = 0ull;
-    summary->max_field = 0ull;
+  }
+}
+
+/*
+ * Largest element of an index / field array, on demand (b200p_block_max): what
+ * RowBlockContainer::Push accumulates per element on the CPU (reference row_block.h:143,153) and
+ * RowBlockIter::NumCol() reports.  Kept out of the emit kernel: streaming Parser users never ask,
+ * and the array is still hot in L2 when a RowBlockIter back-end does.
+ */
+template <typename IdxT>
+__global__ void __launch_bounds__(256) MaxOfArray(const IdxT *values, unsigned long long n,
+                                                  unsigned long long *result) {
+  IdxT m = 0;
+  for (unsigned long long i = blockIdx.x * 256ull + threadIdx.x; i < n; i += gridDim.x * 256ull) {
+    m = MaxOf<IdxT>(m, values[i]);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    m = MaxOf<IdxT>(m, static_cast<IdxT>(__shfl_xor_sync(0xffffffffu, m, d)));
+  }
+  if ((threadIdx.x & 31) == 0 && m != 0) {
+    const volatile unsigned long long *seen = result;
+    if (static_cast<unsigned long long>(m) > *seen) atomicMax(result, static_cast<unsigned long long>(m));
   }
 }
 

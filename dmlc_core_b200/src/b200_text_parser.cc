@@ -60,7 +60,7 @@ class B200TextParser : public Parser<IndexType> {
  public:
   B200TextParser(InputSplit *source, int format, int label_column)
       : source_(source), text_(NULL), handle_(NULL),
-        block_max_index_(0), bytes_read_(0), exhausted_(false) {
+        bytes_read_(0), exhausted_(false) {
     std::memset(&block_, 0, sizeof(block_));
 #if B200_HAVE_TEXT_SPLIT
     text_ = dynamic_cast<TextSplit *>(source);
@@ -121,7 +121,6 @@ class B200TextParser : public Parser<IndexType> {
       Check(b200p_next(handle_, &b));
       bytes_read_ += b.text_bytes;
       if (b.rows == 0) continue;  /* chunks without rows are skipped (reference parser.h:33-38) */
-      block_max_index_ = b.max_index;
       block_.size = static_cast<size_t>(b.rows);
       block_.offset = reinterpret_cast<const size_t *>(b.offset);
       block_.label = b.label;
@@ -136,8 +135,16 @@ class B200TextParser : public Parser<IndexType> {
 
   virtual const RowBlock<IndexType> &Value(void) const { return block_; }
   virtual size_t BytesRead(void) const { return bytes_read_; }
-  /* largest feature index of the current block, reduced on the GPU while index[] was written */
-  uint64_t BlockMaxIndex() const { return block_max_index_; }
+  /* largest feature index of the current block, reduced on the GPU from the array still
+     resident there (b200p_block_max) */
+  void BlockMax(uint64_t *max_index, uint64_t *max_field) {
+    Check(b200p_block_max(handle_, max_index, max_field));
+  }
+  uint64_t BlockMaxIndex() {
+    uint64_t mi = 0, mf = 0;
+    BlockMax(&mi, &mf);
+    return mi;
+  }
 
  private:
   /* keep the pipeline full: read chunks and enqueue them until `depth` are in flight */
@@ -247,7 +254,6 @@ class B200TextParser : public Parser<IndexType> {
 #endif
   b200p_handle handle_;
   RowBlock<IndexType> block_;
-  uint64_t block_max_index_;
   size_t bytes_read_;
   size_t chunk_bytes_;
   int depth_;
@@ -331,8 +337,8 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
   explicit InMemoryRowIter(Parser<IndexType> *parser) : at_head_(true), max_index_(0) {
     offset_.push_back(0);
     const double t0 = GetTime();
-    /* the B200 parser already knows each block's largest index (reduced on the GPU as the
-       array was written); any other parser gets the reference's per-element scan */
+    /* the B200 parser reduces each block's largest index on the GPU, where the array still
+       sits; any other parser gets the reference's per-element scan */
     B200TextParser<IndexType> *gpu = dynamic_cast<B200TextParser<IndexType> *>(parser);
     try {
       while (parser->Next()) {
@@ -510,15 +516,18 @@ class CachedRowIter : public RowBlockIter<IndexType> {
         label_.insert(label_.end(), b.label, b.label + b.size);
         if (b.weight != NULL) weight_.insert(weight_.end(), b.weight, b.weight + b.size);
         if (b.qid != NULL) qid_.insert(qid_.end(), b.qid, b.qid + b.size);
-        if (b.field != NULL) {
-          field_.insert(field_.end(), b.field + base, b.field + base + nnz);
-          for (size_t i = 0; i < nnz; ++i) page_max_field_ = std::max(page_max_field_, b.field[base + i]);
-        }
+        if (b.field != NULL) field_.insert(field_.end(), b.field + base, b.field + base + nnz);
         index_.insert(index_.end(), b.index + base, b.index + base + nnz);
         if (gpu != NULL) {
-          page_max_index_ = std::max(page_max_index_, static_cast<IndexType>(gpu->BlockMaxIndex()));
+          uint64_t mi = 0, mf = 0;
+          gpu->BlockMax(&mi, &mf);
+          page_max_index_ = std::max(page_max_index_, static_cast<IndexType>(mi));
+          page_max_field_ = std::max(page_max_field_, static_cast<IndexType>(mf));
         } else {
           for (size_t i = 0; i < nnz; ++i) page_max_index_ = std::max(page_max_index_, b.index[base + i]);
+          if (b.field != NULL) {
+            for (size_t i = 0; i < nnz; ++i) page_max_field_ = std::max(page_max_field_, b.field[base + i]);
+          }
         }
         if (b.value != NULL) value_.insert(value_.end(), b.value + base, b.value + base + nnz);
         for (size_t i = 1; i <= b.size; ++i) offset_.push_back(shift + b.offset[i] - base);

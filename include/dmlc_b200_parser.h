@@ -82,11 +82,6 @@ typedef struct b200p_rowblock {
   uint64_t text_bytes; /* size of the chunk this block came from (-> Parser::BytesRead) */
   int32_t index_bytes;
   int32_t on_device;   /* 1: pointers are device memory, 0: pinned host memory */
-  /* largest value in index[] / field[] (0 when empty), reduced on the GPU while the arrays are
-     written: what RowBlockContainer::Push accumulates per element on the CPU
-     (src/data/row_block.h:143,153) and RowBlockIter::NumCol() reports (basic_row_iter.h:44) */
-  uint64_t max_index;
-  uint64_t max_field;
 } b200p_rowblock;
 
 /* Replaces: new LibSVMParser<I>(source, nthread) etc. (src/data.cc:21-60). Allocates the
@@ -132,6 +127,15 @@ int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes);
 int b200p_next(b200p_handle h, b200p_rowblock *out);
 /* chunks submitted and not yet returned by b200p_next */
 int b200p_pending(b200p_handle h);
+
+/*
+ * Largest value in index[] and field[] (0 when empty) of the block most recently returned by
+ * b200p_next or b200p_parse_device[_finish] on this handle, reduced on the GPU from the arrays
+ * still resident there. Replaces the per-element max_index / max_field bookkeeping of
+ * RowBlockContainer::Push (src/data/row_block.h:143,153) behind RowBlockIter::NumCol()
+ * (src/data/basic_row_iter.h:44). On demand, because a streaming Parser user never needs it.
+ */
+int b200p_block_max(b200p_handle h, uint64_t *max_index, uint64_t *max_field);
 
 /* Copy nbytes from device memory returned by the device-resident calls into host memory,
    ordered after the handle's stream (for callers that do not link the CUDA runtime).

@@ -147,17 +147,20 @@ def test_corpus_streaming(cuda_lib, oracle, kind, fmt, ib, lc):
 
 @pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA)
 def test_max_index_is_reduced_on_the_gpu(cuda_lib, oracle, kind, fmt, ib, lc):
-    """b200p_rowblock.max_index / max_field = what RowBlockContainer::Push would accumulate."""
+    """b200p_block_max = what RowBlockContainer::Push would accumulate, for both paths."""
     from dmlc_core_b200 import datagen
     from gpu_util import to_device
     data, _ = datagen.generate(kind, 9, 2 << 20)
     exp = oracle.parse_buffer(fmt, data.tobytes(), ib, lc)
     p = _parser(cuda_lib, fmt, ib, lc)
     t, n = to_device(data)
-    for _ in range(2):       # second call: the summary must have been reset
-        blk = p.parse_device(t.data_ptr(), n)
-        assert blk.max_index == int(exp["index"].max())
-        assert blk.max_field == (int(exp["field"].max()) if len(exp["field"]) else 0)
+    want = (int(exp["index"].max()), int(exp["field"].max()) if len(exp["field"]) else 0)
+    for _ in range(2):       # second call: the result words must have been reset
+        p.parse_device(t.data_ptr(), n)
+        assert p.block_max() == want
+    p.submit(data)
+    p.next_raw()
+    assert p.block_max() == want
     p.close()
 
 
@@ -241,7 +244,7 @@ def test_full_size_properties(cuda_lib, oracle, kind, fmt, ib, lc):
     shift = torch.arange(k, device="cuda", dtype=torch.int64).view(k, 1) * nnz1
     assert bool((body - shift == body[0:1]).all()) and int(offset[-1].item()) == nnz1 * k
     assert np.array_equal(body[0].cpu().numpy().view(np.uint64), small["offset"][:-1])
-    assert blk.max_index == int(small["index"].max())
+    assert p.block_max()[0] == int(small["index"].max())
     p.close()
 
 
