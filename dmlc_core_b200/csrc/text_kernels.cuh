@@ -402,19 +402,23 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
   const uint32_t at = entry >> 2;
   const uint32_t kind = entry & 3u;   /* separator kind, see SeparatorKind() */
 
-  /* ---- the separator in front of this token ---- */
-  bool line_start = kind == 3u;  /* separator contains an EOL (or the chunk starts here) */
-  bool bound = kind == 1u;
-  bool qid_a = false, qid_b = false;     /* separator is [blank]*"qid:"... / [space]*"qid:"... */
-  uint32_t qid_at_a = 0, qid_at_b = 0;   /* byte after that "qid:" */
   const bool general = active && kind == 0u;
   const uint32_t general_m = __ballot_sync(0xffffffffu, general);
-  if (!EMIT && general_m == 0u) {
-    /* Counting shortcut.  With only the three simple separator kinds in the group and no chain
-       longer than three tokens, the role counts are plain mask arithmetic on warp-uniform
-       ballots -- no per-lane chain positions.  Anything else takes the general code below,
-       which pass 2 always uses; both implement the same rules (the checked build verifies that
-       pass 2 produces exactly what pass 1 counted). */
+
+  /* role masks of the group (bit i = token i) and the chain context handed to the next group */
+  uint32_t m_label, m_weight, m_index, m_value, m_qid = 0u, m_field = 0u;
+  int next_pos;
+  bool next_first;
+  int prev_pos = 0;   /* general path only: chain position of the token before this one */
+  bool simple = false;
+  uint32_t qid_at = 0;   /* byte after "qid:" when this token follows the probe */
+
+  if (general_m == 0u) {
+    /* Common case.  With only the three simple separator kinds in the group and no chain longer
+       than three tokens, chain positions and roles are plain mask arithmetic on warp-uniform
+       ballots -- no per-lane chain walk.  Longer chains and unusual separators take the general
+       code below; both implement the same rules (the checked build verifies that pass 2
+       produces exactly what pass 1 counted, range by range). */
     const uint32_t act_m = count >= 32u ? 0xffffffffu : ((1u << count) - 1u);
     const uint32_t line_m = __ballot_sync(0xffffffffu, active && kind == 3u);
     const uint32_t bound_m = __ballot_sync(0xffffffffu, active && kind == 1u);
@@ -425,143 +429,152 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
     const uint32_t p3 = bound_m & ((p2 << 1) | c2);               /* chain position 3 */
     const uint32_t p4 = bound_m & ((p3 << 1) | c3);               /* longer chains */
     if (p4 == 0u) {
+      simple = true;
       const uint32_t p2f = p2 & ((line_m << 1) | (c1 & cf));      /* ... in the line's first chain */
       const uint32_t p3f = p3 & ((p2f << 1) | (c2 & cf));
-      uint32_t index_m, value_m;
+      m_label = line_m;
+      m_weight = p2f;
       if (FMT == kLibSVM) {
-        index_m = (start_m & ~line_m) | p3;   /* first chain: label, weight, index; else index, value, index */
-        value_m = p2 & ~p2f;
+        m_index = (start_m & ~line_m) | p3;   /* first chain: label, weight, index; else index, value, index */
+        m_value = p2 & ~p2f;
       } else {
-        index_m = p2 & ~p2f;                  /* field:index[:value]; a first-chain position 3 opens */
-        value_m = p3 & ~p3f;                  /* a triple that no index follows: dropped */
+        m_field = (start_m & ~line_m) | p3f;  /* field candidates (converted even when dropped) */
+        m_index = p2 & ~p2f;                  /* field:index[:value] */
+        m_value = p3 & ~p3f;
       }
-      st.seen[kRows] += __popc(line_m);
-      st.seen[kNnz] += __popc(index_m);
-      st.seen[kValues] += __popc(value_m);
-      st.seen[kWeights] += __popc(p2f);
       const uint32_t last = 1u << (count - 1u);
-      st.carry_pos = (p3 & last) ? 3 : ((p2 & last) ? 2 : 1);
-      st.carry_first = ((line_m | p2f | p3f) & last) != 0u;
-      st.carry_at = __shfl_sync(0xffffffffu, at, static_cast<int>(count) - 1);
-      return;
+      next_pos = (p3 & last) ? 3 : ((p2 & last) ? 2 : 1);
+      next_first = ((line_m | p2f | p3f) & last) != 0u;
     }
   }
-  if (general_m != 0u) {
-    /* not one of the three common separators: walk back over it */
-    /* the one longer separator that well-formed ranking data has on every row,
-       "<digit-run byte> qid:" (libsvm_parser.h:66-75), is recognised without the walk */
-    bool walk = general;
-    if (FMT == kLibSVM && general && at >= 6u) {
-      if (txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
-          txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u))) {
-        line_start = false;
-        bound = false;            /* first non-blank of the separator is 'q' */
-        qid_a = qid_b = true;     /* one space, then "qid:": both probe variants match */
-        qid_at_a = qid_at_b = at;
-        walk = false;
-      }
-    }
-    if (walk) {
-      line_start = true;
-      const uint32_t kQid = (uint32_t(':') << 24) | (uint32_t('d') << 16) | (uint32_t('i') << 8) |
-                            uint32_t('q');
-      uint32_t first_nonblank = 0, window = 0;
-      bool in_a = false, in_b = false;
-      uint32_t q = at;
-      for (;;) {
-        if (q == 0u) break;               /* start of chunk: a line starts here */
-        --q;
-        const uint32_t c = txt.at(q);
-        if (IsEol(c)) break;
-        if (IsDigitChar(c)) {             /* previous token ends at q */
+
+  if (!simple) {
+    /* ---- the separator in front of this token ---- */
+    bool line_start = kind == 3u;  /* separator contains an EOL (or the chunk starts here) */
+    bool bound = kind == 1u;
+    bool qid_a = false, qid_b = false;     /* separator is [blank]*"qid:"... / [space]*"qid:"... */
+    uint32_t qid_at_a = 0, qid_at_b = 0;   /* byte after that "qid:" */
+    if (general_m != 0u) {
+      /* the one longer separator that well-formed ranking data has on every row,
+         "<digit-run byte> qid:" (libsvm_parser.h:66-75), is recognised without the walk */
+      bool walk = general;
+      if (FMT == kLibSVM && general && at >= 6u) {
+        if (txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
+            txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u))) {
           line_start = false;
-          bound = (first_nonblank == ':');
+          bound = false;            /* first non-blank of the separator is 'q' */
+          qid_a = qid_b = true;     /* one space, then "qid:": both probe variants match */
+          qid_at_a = qid_at_b = at;
+          walk = false;
+        }
+      }
+      if (walk) {
+        /* anything else: walk back over the separator */
+        line_start = true;
+        const uint32_t kQid = (uint32_t(':') << 24) | (uint32_t('d') << 16) | (uint32_t('i') << 8) |
+                              uint32_t('q');
+        uint32_t first_nonblank = 0, window = 0;
+        bool in_a = false, in_b = false;
+        uint32_t q = at;
+        for (;;) {
+          if (q == 0u) break;               /* start of chunk: a line starts here */
+          --q;
+          const uint32_t c = txt.at(q);
+          if (IsEol(c)) break;
+          if (IsDigitChar(c)) {             /* previous token ends at q */
+            line_start = false;
+            bound = (first_nonblank == ':');
+            if (FMT == kLibSVM) {
+              if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; }
+              if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; }
+            }
+            break;
+          }
+          const bool space = (c == ' ');
+          const bool blank = space || c == '\t';
+          if (!blank) first_nonblank = c;
           if (FMT == kLibSVM) {
-            if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; }
-            if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; }
+            /* leading-separator tracking for "qid:" (libsvm_parser.h:66-75): after `label` the
+               reference has skipped blanks, after `label:weight` only spaces */
+            if (blank) {
+              if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; in_a = true; }
+            } else {
+              in_a = false; qid_a = false;
+            }
+            if (space) {
+              if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; in_b = true; }
+            } else {
+              in_b = false; qid_b = false;
+            }
+            window = (window << 8) | c;
           }
-          break;
-        }
-        const bool space = (c == ' ');
-        const bool blank = space || c == '\t';
-        if (!blank) first_nonblank = c;
-        if (FMT == kLibSVM) {
-          /* leading-separator tracking for "qid:" (libsvm_parser.h:66-75): after `label` the
-             reference has skipped blanks, after `label:weight` only spaces */
-          if (blank) {
-            if (!in_a) { qid_a = (window == kQid); qid_at_a = q + 5u; in_a = true; }
-          } else {
-            in_a = false; qid_a = false;
-          }
-          if (space) {
-            if (!in_b) { qid_b = (window == kQid); qid_at_b = q + 5u; in_b = true; }
-          } else {
-            in_b = false; qid_b = false;
-          }
-          window = (window << 8) | c;
         }
       }
     }
-  }
 
-  /* ---- chain position and role, by ballot ---- */
-  const uint32_t act_m = __ballot_sync(0xffffffffu, active);
-  const uint32_t nl_m = __ballot_sync(0xffffffffu, active && line_start);
-  const uint32_t bd_m = __ballot_sync(0xffffffffu, active && bound);
-  const uint32_t starts = act_m & ~bd_m;              /* tokens that open a chain */
-  const uint32_t below = starts & LaneMaskLe();
-  int pos;
-  bool first;
-  if (below != 0u) {
-    const int j = 31 - __clz(below);
-    pos = lane - j + 1;
-    first = (nl_m >> j) & 1u;
-  } else {
-    pos = st.carry_pos + lane + 1;
-    first = st.carry_first;
-  }
-  int prev_pos = __shfl_up_sync(0xffffffffu, pos, 1);
-  int prev_first = __shfl_up_sync(0xffffffffu, static_cast<int>(first), 1);
-  uint32_t prev_at = __shfl_up_sync(0xffffffffu, at, 1);
-  if (lane == 0) {
-    prev_pos = st.carry_pos;
-    prev_first = st.carry_first;
-    prev_at = st.carry_at;
-  }
-
-  bool is_label = false, is_weight = false, is_index = false, is_value = false, is_field = false;
-  if (active) {
-    if (first && pos == 1) {
-      is_label = true;
-    } else if (first && pos == 2) {
-      is_weight = true;
+    /* ---- chain position and role, by ballot ---- */
+    const uint32_t act_m = __ballot_sync(0xffffffffu, active);
+    const uint32_t nl_m = __ballot_sync(0xffffffffu, active && line_start);
+    const uint32_t bd_m = __ballot_sync(0xffffffffu, active && bound);
+    const uint32_t starts = act_m & ~bd_m;              /* tokens that open a chain */
+    const uint32_t below = starts & LaneMaskLe();
+    int pos;
+    bool first;
+    if (below != 0u) {
+      const int j = 31 - __clz(below);
+      pos = lane - j + 1;
+      first = (nl_m >> j) & 1u;
     } else {
-      const int k = first ? pos - 3 : pos - 1;
-      if (FMT == kLibSVM) {
-        is_index = (k & 1) == 0;
-        is_value = !is_index;
+      pos = st.carry_pos + lane + 1;
+      first = st.carry_first;
+    }
+    prev_pos = __shfl_up_sync(0xffffffffu, pos, 1);
+    int prev_first = __shfl_up_sync(0xffffffffu, static_cast<int>(first), 1);
+    if (lane == 0) {
+      prev_pos = st.carry_pos;
+      prev_first = st.carry_first;
+    }
+    bool is_label = false, is_weight = false, is_index = false, is_value = false, is_field = false;
+    if (active) {
+      if (first && pos == 1) {
+        is_label = true;
+      } else if (first && pos == 2) {
+        is_weight = true;
       } else {
-        const int r = k % 3;
-        is_field = r == 0;   /* emitted only if an index follows: done by the index token */
-        is_index = r == 1;
-        is_value = r == 2;
+        const int k = first ? pos - 3 : pos - 1;
+        if (FMT == kLibSVM) {
+          is_index = (k & 1) == 0;
+          is_value = !is_index;
+        } else {
+          const int r = k % 3;
+          is_field = r == 0;   /* emitted only if an index follows: done by the index token */
+          is_index = r == 1;
+          is_value = r == 2;
+        }
       }
     }
+    bool is_qid = false;
+    if (FMT == kLibSVM) {
+      is_qid = active && !line_start && !bound && prev_first && prev_pos <= 2 &&
+               (prev_pos == 1 ? qid_a : qid_b);
+      qid_at = (prev_pos == 1) ? qid_at_a : qid_at_b;
+    }
+    m_label = __ballot_sync(0xffffffffu, is_label);
+    m_weight = __ballot_sync(0xffffffffu, is_weight);
+    m_index = __ballot_sync(0xffffffffu, is_index);
+    m_value = __ballot_sync(0xffffffffu, is_value);
+    if (FMT == kLibSVM) m_qid = __ballot_sync(0xffffffffu, is_qid);
+    if (FMT == kLibFM) m_field = __ballot_sync(0xffffffffu, is_field);
+    const int last = static_cast<int>(count) - 1;
+    next_pos = __shfl_sync(0xffffffffu, pos, last);
+    next_first = __shfl_sync(0xffffffffu, static_cast<int>(first), last) != 0;
   }
-  bool is_qid = false;
-  if (FMT == kLibSVM) {
-    is_qid = active && !line_start && !bound && prev_first && prev_pos <= 2 &&
-             (prev_pos == 1 ? qid_a : qid_b);
-  }
-
-  const uint32_t lt = LaneMaskLt();
-  const uint32_t m_label = __ballot_sync(0xffffffffu, is_label);
-  const uint32_t m_weight = __ballot_sync(0xffffffffu, is_weight);
-  const uint32_t m_index = __ballot_sync(0xffffffffu, is_index);
-  const uint32_t m_value = __ballot_sync(0xffffffffu, is_value);
-  const uint32_t m_qid = FMT == kLibSVM ? __ballot_sync(0xffffffffu, is_qid) : 0u;
 
   if (EMIT) {
+    const uint32_t lt = LaneMaskLt();
+    const uint32_t me = 1u << lane;
+    const bool is_label = (m_label & me) != 0u, is_weight = (m_weight & me) != 0u;
+    const bool is_index = (m_index & me) != 0u, is_value = (m_value & me) != 0u;
     /* row pointer: a label token opens row r; offset[r] = features stored before it
        (libsvm_parser.h:62-64 push the running index count) */
     if (is_label) {
@@ -569,7 +582,7 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
       prm.offset[st.seen[kRows] + __popc(m_label & lt)] =
           static_cast<unsigned long long>(st.seen[kNnz] + __popc(m_index & lt));
     }
-    if (FMT == kLibFM && is_field && txt.at(at) == '-') {
+    if (FMT == kLibFM && (m_field & me) != 0u && txt.at(at) == '-') {
       /* a field id is converted before the reference knows whether the triple is kept
          (libfm_parser.h:73), so a '-' raises even on a token that is then dropped */
       st.error |= kErrNegativeIndex;
@@ -582,20 +595,29 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
       B200P_CHECK(prm, st.n_weight + __popc(m_weight & lt) < kRoleQueue)
       ws.q_weight[st.n_weight + __popc(m_weight & lt)] = at;
     }
-    if (is_index) {
-      const uint32_t slot = st.n_index + __popc(m_index & lt);
-      B200P_CHECK(prm, slot < kRoleQueue) {
-        ws.q_index[slot] = at;
-        if (FMT == kLibFM) ws.q_field[slot] = prev_at;
+    if (FMT == kLibFM) {
+      /* the field id of a triple is the token in front of its index token */
+      uint32_t prev_at = __shfl_up_sync(0xffffffffu, at, 1);
+      if (lane == 0) prev_at = st.carry_at;
+      if (is_index) {
+        const uint32_t slot = st.n_index + __popc(m_index & lt);
+        B200P_CHECK(prm, slot < kRoleQueue) {
+          ws.q_index[slot] = at;
+          ws.q_field[slot] = prev_at;
+        }
       }
+    } else if (is_index) {
+      const uint32_t slot = st.n_index + __popc(m_index & lt);
+      B200P_CHECK(prm, slot < kRoleQueue)
+      ws.q_index[slot] = at;
     }
     if (is_value) {
       B200P_CHECK(prm, st.n_value + __popc(m_value & lt) < kRoleQueue)
       ws.q_value[st.n_value + __popc(m_value & lt)] = at;
     }
-    if (FMT == kLibSVM && is_qid) {
+    if (FMT == kLibSVM && (m_qid & me) != 0u) {
       B200P_CHECK(prm, st.n_qid + __popc(m_qid & lt) < kRoleQueue)
-      ws.q_qid[st.n_qid + __popc(m_qid & lt)] = (prev_pos == 1) ? qid_at_a : qid_at_b;
+      ws.q_qid[st.n_qid + __popc(m_qid & lt)] = qid_at;
     }
     st.n_label += __popc(m_label);
     st.n_weight += __popc(m_weight);
@@ -610,10 +632,9 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
   st.seen[kWeights] += __popc(m_weight);
   st.seen[kQids] += __popc(m_qid);
 
-  const int last = static_cast<int>(count) - 1;
-  st.carry_pos = __shfl_sync(0xffffffffu, pos, last);
-  st.carry_first = __shfl_sync(0xffffffffu, static_cast<int>(first), last) != 0;
-  st.carry_at = __shfl_sync(0xffffffffu, at, last);
+  st.carry_pos = next_pos;
+  st.carry_first = next_first;
+  st.carry_at = __shfl_sync(0xffffffffu, at, static_cast<int>(count) - 1);
 
   if (EMIT) DrainRoleQueues<FMT, IdxT>(prm, txt, ws, st, lane, false);
 }
