@@ -46,11 +46,23 @@ static int EnvInt(const char *name, int fallback) {
   return (v != NULL && *v != '\0') ? std::atoi(v) : fallback;
 }
 
+/* DMLC_B200_DEVICE: a CUDA ordinal (one process per GPU, the usual launch), or "auto" =
+   part_index modulo DMLC_B200_NUM_DEVICES (default 8), for a single process that opens one
+   parser per part and wants them spread over the GPUs of the box. */
+static int DeviceFor(unsigned part_index) {
+  const char *v = std::getenv("DMLC_B200_DEVICE");
+  if (v != NULL && std::strcmp(v, "auto") == 0) {
+    const int n = std::max(1, EnvInt("DMLC_B200_NUM_DEVICES", 8));
+    return static_cast<int>(part_index % static_cast<unsigned>(n));
+  }
+  return EnvInt("DMLC_B200_DEVICE", 0);
+}
+
 /*
  * One parser instance = one partition of the input on one GPU.
  * Environment knobs (GPU-side settings cannot ride in the URI: CSVParserParam::Init rejects
  * unknown keys, reference csv_parser.h:50 + parameter.h:405-418):
- *   DMLC_B200_DEVICE    CUDA device ordinal (default 0)
+ *   DMLC_B200_DEVICE    CUDA device ordinal (default 0), or "auto" = part_index % DMLC_B200_NUM_DEVICES
  *   DMLC_B200_CHUNK_MB  chunk size in MiB (default 64; the reference uses 8, input_split_base.h:40)
  *   DMLC_B200_DEPTH     chunks in flight (default 3)
  *   DMLC_B200_READ_THREADS  threads of one parallel pread (default: half the cores, at most 8)
@@ -58,7 +70,7 @@ static int EnvInt(const char *name, int fallback) {
 template <typename IndexType>
 class B200TextParser : public Parser<IndexType> {
  public:
-  B200TextParser(InputSplit *source, int format, int label_column)
+  B200TextParser(InputSplit *source, int format, int label_column, unsigned part_index = 0)
       : source_(source), text_(NULL), handle_(NULL),
         bytes_read_(0), exhausted_(false) {
     std::memset(&block_, 0, sizeof(block_));
@@ -70,7 +82,7 @@ class B200TextParser : public Parser<IndexType> {
     cfg.format = format;
     cfg.index_bytes = static_cast<int32_t>(sizeof(IndexType));
     cfg.label_column = label_column;
-    cfg.device = EnvInt("DMLC_B200_DEVICE", 0);
+    cfg.device = DeviceFor(part_index);
     chunk_bytes_ = static_cast<size_t>(std::max(1, EnvInt("DMLC_B200_CHUNK_MB", 64))) << 20;
     chunk_bytes_ = std::min<size_t>(chunk_bytes_, B200P_MAX_CHUNK_BYTES);
     cfg.chunk_bytes = chunk_bytes_;
@@ -273,7 +285,7 @@ Parser<IndexType> *CreateLibSVMParser(const std::string &path,
                                       const std::map<std::string, std::string> &args,
                                       unsigned part_index, unsigned num_parts) {
   InputSplit *source = InputSplit::Create(path.c_str(), part_index, num_parts, "text");
-  return new B200TextParser<IndexType>(source, B200P_FORMAT_LIBSVM, -1);
+  return new B200TextParser<IndexType>(source, B200P_FORMAT_LIBSVM, -1, part_index);
 }
 
 template <typename IndexType>
@@ -281,7 +293,7 @@ Parser<IndexType> *CreateLibFMParser(const std::string &path,
                                      const std::map<std::string, std::string> &args,
                                      unsigned part_index, unsigned num_parts) {
   InputSplit *source = InputSplit::Create(path.c_str(), part_index, num_parts, "text");
-  return new B200TextParser<IndexType>(source, B200P_FORMAT_LIBFM, -1);
+  return new B200TextParser<IndexType>(source, B200P_FORMAT_LIBFM, -1, part_index);
 }
 
 template <typename IndexType>
@@ -310,7 +322,7 @@ Parser<IndexType> *CreateCSVParser(const std::string &path,
     }
   }
   InputSplit *source = InputSplit::Create(path.c_str(), part_index, num_parts, "text");
-  return new B200TextParser<IndexType>(source, B200P_FORMAT_CSV, label_column);
+  return new B200TextParser<IndexType>(source, B200P_FORMAT_CSV, label_column, part_index);
 }
 
 /* type lookup: reference CreateParser_, src/data.cc:62-85 */

@@ -183,3 +183,31 @@ def test_disk_cache_round_trip_with_the_reference(hostapi, reference, oracle, tm
         again, ncol2, _ = hostapi.row_iter(uri, 0, 1, fmt, ib, passes=2)
         assert same_rowblocks(again, exp) is None and ncol2 == ncol
         assert os.path.getsize(cache) == size
+
+
+def test_two_parsers_interleaved_in_one_process(hostapi, oracle, tmp_path, monkeypatch):
+    """One process, one parser per part (DMLC_B200_DEVICE=auto spreads them over the box's GPUs;
+    with a single GPU both land on device 0): handles are independent, calls may interleave."""
+    from dmlc_core_b200 import datagen
+    monkeypatch.setenv("DMLC_B200_DEVICE", "auto")
+    monkeypatch.setenv("DMLC_B200_NUM_DEVICES", "1")
+    monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
+    data, rows = datagen.generate("libfm", 23, 4 << 20)
+    f = tmp_path / "fm.txt"
+    f.write_bytes(data.tobytes())
+    parsers = [hostapi.CppParser(str(f), k, 2, "libfm", 8) for k in range(2)]
+    blocks = [[], []]
+    live = [True, True]
+    while any(live):
+        for k in range(2):
+            if live[k]:
+                b = parsers[k].next()
+                if b is None:
+                    live[k] = False
+                else:
+                    blocks[k].append(b)
+    for k in range(2):
+        exp = oracle.parse_files("libfm", [str(f)], k, 2, 8)
+        got = hostapi.concat_blocks(blocks[k], 8)
+        assert same_rowblocks(got, exp) is None, k
+        parsers[k].close()
