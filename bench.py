@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--block-mb", type=int, default=1000, help="unique generated block (MB)")
     ap.add_argument("--chunk-mb", type=int, default=64, help="e2e chunk size (MiB)")
     ap.add_argument("--range-bytes", type=int, default=0)
+    ap.add_argument("--depth", type=int, default=3, help="e2e chunks in flight")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -365,7 +366,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         pe = Parser("csv", index_bytes=4, label_column=LABEL_COLUMN, device=local,
-                    range_bytes=args.range_bytes, chunk_bytes=args.chunk_mb << 20, depth=3)
+                    range_bytes=args.range_bytes, chunk_bytes=args.chunk_mb << 20, depth=args.depth)
         base_ptr = harr.ctypes.data
         d2h = [0]
 
@@ -373,7 +374,7 @@ def main():
             got_rows = 0
             for _ in range(copies):
                 for (a, b) in chunks:
-                    while pe.pending() >= 3:
+                    while pe.pending() >= args.depth:
                         r = pe.next_raw()
                         got_rows += r.rows
                         d2h[0] += 8 * (r.rows + 1) + 4 * r.rows + 8 * r.nnz
@@ -397,7 +398,7 @@ def main():
         barrier()
         e2e = {"value": world * text_bytes / e2e_s / GB, "unit": "GB/s",
                "h2d_bytes_per_step": text_bytes, "d2h_bytes_per_step": d2h[0] // e2e_steps,
-               "ms_per_step": e2e_s * 1e3, "chunk_bytes": args.chunk_mb << 20, "depth": 3,
+               "ms_per_step": e2e_s * 1e3, "chunk_bytes": args.chunk_mb << 20, "depth": args.depth,
                "api": "b200p_submit / b200p_next (pinned host text in, pinned host CSR out)",
                "link": link,
                "frac_of_h2d_link_under_duplex": (text_bytes / e2e_s / GB) / link["h2d_with_concurrent_d2h_GBps"]}
