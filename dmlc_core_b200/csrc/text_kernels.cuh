@@ -699,7 +699,12 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
  * byte range [w * range_bytes, (w+1) * range_bytes): the lines whose first byte lies in it.
  */
 template <int FMT, typename IdxT, bool EMIT>
-__global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
+#ifdef B200P_MIN_CTAS   /* tuning experiments only; the default leaves the register budget to ptxas */
+#define B200P_WALK_BOUNDS __launch_bounds__(kCtaThreads, B200P_MIN_CTAS)
+#else
+#define B200P_WALK_BOUNDS __launch_bounds__(kCtaThreads)
+#endif
+__global__ void B200P_WALK_BOUNDS WalkText(const WalkParams prm) {
   __shared__ WarpScratch<FMT> scratch[kWarpsPerCta];
   __shared__ __align__(16) uint8_t lut[256];
   static_assert(kCtaThreads == 256, "one thread fills one entry of the class table");
@@ -764,16 +769,34 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
     uint32_t carry = FMT == kCSV ? 3u : 0x20u;
     bool done = false;
     uint32_t csv_fields = 0, csv_rows = 0; /* per-lane tallies of the CSV counting shortcut */
+    /* interior step: wholly owned, wholly inside the chunk, and too early to hold the EOL
+       that closes the region -- no masks, no bounds checks (30 of 32 steps of a 16 KiB range).
+       CSV pass 2 requests its 16 bytes per lane one step ahead, so the HBM latency is spent behind
+       the previous step's conversions (-3 % on B200); the other walks are tighter on registers and
+       measured slower that way, so they load in place. */
+    constexpr bool kAhead = (FMT == kCSV) && EMIT;
+    const auto is_interior = [&](uint32_t b) { return b >= begin && b + kStepBytes <= hi - 1u; };
+    const uint8_t *const my_text = prm.text + 16u * lane;
+    uint4 ahead = make_uint4(0u, 0u, 0u, 0u);
+    if (kAhead && is_interior(begin & ~uint32_t(kStepBytes - 1))) {
+      ahead = __ldg(reinterpret_cast<const uint4 *>(my_text + (begin & ~uint32_t(kStepBytes - 1))));
+    }
     for (uint32_t base = begin & ~uint32_t(kStepBytes - 1); !done; base += kStepBytes) {
       const uint32_t first_byte = base + 16u * lane;
-      /* interior step: wholly owned, wholly inside the chunk, and too early to hold the EOL
-         that closes the region -- no masks, no bounds checks (30 of 32 steps of a 16 KiB range) */
-      const bool interior = base >= begin && base + kStepBytes <= hi - 1u;
+      const bool interior = is_interior(base);
+      uint4 now = ahead;
+      if constexpr (kAhead) {
+        if (is_interior(base + kStepBytes)) {
+          ahead = __ldg(reinterpret_cast<const uint4 *>(my_text + base + kStepBytes));
+        }
+      } else {
+        if (interior) now = __ldg(reinterpret_cast<const uint4 *>(my_text + base));
+      }
       if constexpr (FMT == kCSV) {
         uint32_t cls;             /* interleaved class mask of my 16 bytes */
         uint32_t keep = kEven;    /* owned bytes, on the even bits */
         if (interior) {
-          cls = ClassifyLut(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), lut, prm.four);
+          cls = ClassifyLut(now, lut, prm.four);
         } else {
           cls = ClassifyLut(Load16(prm.text, prm.size, first_byte), lut, prm.four);
           /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
@@ -828,8 +851,7 @@ __global__ void __launch_bounds__(kCtaThreads) WalkText(const WalkParams prm) {
         uint32_t m0, m1;                               /* class nibbles of bytes 0..7 / 8..15 */
         uint32_t k0 = 0xffffffffu, k1 = 0xffffffffu;   /* owned bytes, as nibbles */
         if (interior) {
-          ClassifyLut4(__ldg(reinterpret_cast<const uint4 *>(prm.text + first_byte)), lut, prm.sixteen,
-                       &m0, &m1);
+          ClassifyLut4(now, lut, prm.sixteen, &m0, &m1);
         } else {
           ClassifyLut4(Load16(prm.text, prm.size, first_byte), lut, prm.sixteen, &m0, &m1);
           /* does the owned region close inside this step?  (first EOL at or after hi - 1) */
