@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--chunk-mb", type=int, default=64, help="e2e chunk size (MiB)")
     ap.add_argument("--range-bytes", type=int, default=0)
     ap.add_argument("--depth", type=int, default=3, help="e2e chunks in flight")
+    ap.add_argument("--host-threads", type=int, default=-1,
+                    help="e2e: b200p_set_host_threads (-1 = library default, 0 = copy index[] back)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -368,36 +370,46 @@ def main():
         pe = Parser("csv", index_bytes=4, label_column=LABEL_COLUMN, device=local,
                     range_bytes=args.range_bytes, chunk_bytes=args.chunk_mb << 20, depth=args.depth)
         base_ptr = harr.ctypes.data
-        d2h = [0]
+        if args.host_threads >= 0:
+            pe.set_host_threads(args.host_threads)
+
+        handed = [0]   # bytes of the arrays handed to the caller (all seven, host memory)
+
+        def take():
+            r = pe.next_raw()
+            handed[0] += 8 * (r.rows + 1) + 4 * r.rows + 8 * r.nnz
+            return r.rows
 
         def e2e_step():
             got_rows = 0
             for _ in range(copies):
                 for (a, b) in chunks:
                     while pe.pending() >= args.depth:
-                        r = pe.next_raw()
-                        got_rows += r.rows
-                        d2h[0] += 8 * (r.rows + 1) + 4 * r.rows + 8 * r.nnz
+                        got_rows += take()
                     pe.submit_in_place(base_ptr + a, b - a)
             while pe.pending():
-                r = pe.next_raw()
-                got_rows += r.rows
-                d2h[0] += 8 * (r.rows + 1) + 4 * r.rows + 8 * r.nnz
+                got_rows += take()
             return got_rows
 
         e2e_steps = max(1, min(args.steps, 3))
         assert e2e_step() == rows * copies
         e2e_step()
         barrier()
-        d2h[0] = 0
+        up0, down0 = pe.copied_bytes()   # the library's own count of what crossed the link
+        handed[0] = 0
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             e2e_step()
         torch.cuda.synchronize()
         e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
+        up1, down1 = pe.copied_bytes()
         barrier()
         e2e = {"value": world * text_bytes / e2e_s / GB, "unit": "GB/s",
-               "h2d_bytes_per_step": text_bytes, "d2h_bytes_per_step": d2h[0] // e2e_steps,
+               "h2d_bytes_per_step": (up1 - up0) // e2e_steps,
+               "d2h_bytes_per_step": (down1 - down0) // e2e_steps,
+               "result_bytes_per_step": handed[0] // e2e_steps,
+               "index_rebuilt_on_host": (down1 - down0) < handed[0],
+               "host_threads": args.host_threads if args.host_threads >= 0 else "library default (<= 4)",
                "ms_per_step": e2e_s * 1e3, "chunk_bytes": args.chunk_mb << 20, "depth": args.depth,
                "api": "b200p_submit / b200p_next (pinned host text in, pinned host CSR out)",
                "link": link,

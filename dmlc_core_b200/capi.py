@@ -24,6 +24,7 @@ EXPORTS = (
     "b200p_create", "b200p_destroy", "b200p_last_error", "b200p_parse_device",
     "b200p_parse_device_async", "b200p_parse_device_finish", "b200p_input_buffer",
     "b200p_submit", "b200p_next", "b200p_pending", "b200p_fetch", "b200p_launch_count",
+    "b200p_set_host_threads", "b200p_copied_bytes",
     "b200p_set_profiling", "b200p_kernel_time", "b200p_version", "b200p_parse_device_noalloc",
     "b200p_block_max",
 )
@@ -92,6 +93,10 @@ def load():
     lib.b200p_pending.restype = C.c_int
     lib.b200p_fetch.argtypes = [H, C.c_void_p, C.c_void_p, C.c_uint64]
     lib.b200p_fetch.restype = C.c_int
+    lib.b200p_set_host_threads.argtypes = [H, C.c_int]
+    lib.b200p_set_host_threads.restype = C.c_int
+    lib.b200p_copied_bytes.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.b200p_copied_bytes.restype = C.c_int
     lib.b200p_block_max.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.b200p_block_max.restype = C.c_int
     lib.b200p_launch_count.argtypes = [H]
@@ -255,6 +260,16 @@ class Parser(object):
 
     def launch_count(self):
         return int(self.lib.b200p_launch_count(self.handle))
+
+    def set_host_threads(self, threads):
+        """Host threads that rebuild CSV column ids in next(); 0 = always copy them from the GPU."""
+        self._check(self.lib.b200p_set_host_threads(self.handle, int(threads)))
+
+    def copied_bytes(self):
+        """(host-to-device, device-to-host) bytes this handle has moved over the link."""
+        up, down = C.c_uint64(0), C.c_uint64(0)
+        self._check(self.lib.b200p_copied_bytes(self.handle, C.byref(up), C.byref(down)))
+        return int(up.value), int(down.value)
 
     def parse_host(self, data):
         """submit + next for one chunk; raises ParseError where the reference would throw."""

@@ -9,11 +9,16 @@
 #include <pthread.h>
 
 #include <algorithm>
+#include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <functional>
+#include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/dmlc_b200_parser.h"
@@ -59,8 +64,88 @@ struct Slot {
   const uint8_t *text; /* device pointer of the chunk in flight */
   uint64_t nbytes;
   bool busy;
+  cudaEvent_t offsets_home; /* streaming path: offset[] has reached the host (created on first use) */
   Slot() { std::memset(this, 0, sizeof(*this)); }
 };
+
+/*
+ * A few host threads for the one piece of per-element host work in the library: rebuilding the
+ * column ids of wide CSV rows from offset[] instead of bringing them back over PCIe (b200p_next).
+ * Run(parts, fn) calls fn(0..parts-1) once each, the calling thread included, and returns when
+ * all are done.
+ */
+class HostPool {
+ public:
+  explicit HostPool(int threads) : fn_(NULL), parts_(0), next_(0), left_(0), epoch_(0), stop_(false) {
+    for (int i = 1; i < threads; ++i) workers_.emplace_back([this] { Work(); });
+  }
+  ~HostPool() {
+    {
+      std::lock_guard<std::mutex> g(m_);
+      stop_ = true;
+    }
+    wake_.notify_all();
+    for (std::thread &t : workers_) t.join();
+  }
+  int threads() const { return static_cast<int>(workers_.size()) + 1; }
+  void Run(int parts, const std::function<void(int)> &fn) {
+    std::unique_lock<std::mutex> g(m_);
+    fn_ = &fn;
+    parts_ = parts;
+    next_ = 0;
+    left_ = parts;
+    ++epoch_;
+    wake_.notify_all();
+    Drain(&g);
+    idle_.wait(g, [this] { return left_ == 0; });
+    fn_ = NULL;
+  }
+
+ private:
+  void Drain(std::unique_lock<std::mutex> *g) { /* called with the lock held */
+    while (fn_ != NULL && next_ < parts_) {
+      const int mine = next_++;
+      const std::function<void(int)> *fn = fn_;
+      g->unlock();
+      (*fn)(mine);
+      g->lock();
+      if (--left_ == 0) idle_.notify_all();
+    }
+  }
+  void Work() {
+    std::unique_lock<std::mutex> g(m_);
+    uint64_t seen = 0;
+    for (;;) {
+      wake_.wait(g, [&] { return stop_ || epoch_ != seen; });
+      if (stop_) return;
+      seen = epoch_;
+      Drain(&g);
+    }
+  }
+  std::vector<std::thread> workers_;
+  std::mutex m_;
+  std::condition_variable wake_, idle_;
+  const std::function<void(int)> *fn_;
+  int parts_, next_, left_;
+  uint64_t epoch_;
+  bool stop_;
+};
+
+/* index[offset[r] + j] = j for the rows [r0, r1): what CSVParser::ParseBlock stores as the
+   column id of the j-th non-label field of a row (reference csv_parser.h:84-88) */
+template <typename T>
+static void CsvColumnIds(const unsigned long long *offset, uint64_t r0, uint64_t r1, T *index,
+                         const T *iota, uint64_t iota_len) {
+  for (uint64_t r = r0; r < r1; ++r) {
+    const uint64_t len = offset[r + 1] - offset[r];
+    T *dst = index + offset[r];
+    if (len <= iota_len) {
+      std::memcpy(dst, iota, len * sizeof(T));
+    } else {
+      for (uint64_t j = 0; j < len; ++j) dst[j] = static_cast<T>(j);
+    }
+  }
+}
 
 }  // namespace b200p
 
@@ -80,6 +165,10 @@ struct b200p_parser_s {
   double rows_per_byte, nnz_per_byte; /* densest chunk seen so far: sizes later allocations */
   uint64_t launches;
   unsigned long long *d_max; /* two words for b200p_block_max, allocated on first use */
+  int host_threads;          /* b200p_set_host_threads; 0 = column ids always come from the GPU */
+  HostPool *pool;            /* created on first use */
+  std::vector<uint64_t> iota; /* 0, 1, 2, ... in the handle's index width */
+  uint64_t copied_h2d, copied_d2h;
   /* optional per-kernel timing (b200p_set_profiling): event pairs around each launch */
   bool profiling;
   struct Timed { int kind; cudaEvent_t start, stop; };
@@ -399,6 +488,7 @@ static void DestroySlot(Slot *s) {
   cudaFreeHost(s->h_summary);
   FreeDeviceArrays(&s->dev);
   FreeHostArrays(&s->host);
+  if (s->offsets_home != NULL) cudaEventDestroy(s->offsets_home);
   if (s->own_stream && s->stream != NULL) cudaStreamDestroy(s->stream);
   *s = Slot();
 }
@@ -415,6 +505,35 @@ static int InitSlot(b200p_handle h, Slot *s, cudaStream_t stream) {
   CUDA_TRY(h, cudaHostAlloc(reinterpret_cast<void **>(&s->h_summary), sizeof(ChunkSummary), cudaHostAllocDefault));
   std::memset(s->h_summary, 0, sizeof(ChunkSummary));
   return B200P_OK;
+}
+
+/* host.index of a CSV chunk from host.offset (already on the host), spread over the pool */
+static void RebuildCsvIndex(b200p_handle h, Slot *s, uint64_t rows) {
+  const bool wide = h->cfg.index_bytes == 8;
+  const uint64_t kIota = 4096;
+  if (h->iota.empty()) {
+    h->iota.resize(wide ? kIota : kIota / 2);
+    if (wide) {
+      for (uint64_t j = 0; j < kIota; ++j) h->iota[j] = j;
+    } else {
+      uint32_t *narrow = reinterpret_cast<uint32_t *>(h->iota.data());
+      for (uint64_t j = 0; j < kIota; ++j) narrow[j] = static_cast<uint32_t>(j);
+    }
+  }
+  if (h->pool == NULL) h->pool = new HostPool(h->host_threads);
+  const int parts = static_cast<int>(std::min<uint64_t>(rows, 4ull * h->pool->threads()));
+  const unsigned long long *offset = s->host.offset;
+  void *index = s->host.index;
+  const uint64_t *iota = h->iota.data();
+  h->pool->Run(parts, [=](int part) {
+    const uint64_t r0 = rows * part / parts, r1 = rows * (part + 1) / parts;
+    if (wide) {
+      CsvColumnIds(offset, r0, r1, static_cast<uint64_t *>(index), iota, kIota);
+    } else {
+      CsvColumnIds(offset, r0, r1, static_cast<uint32_t *>(index),
+                   reinterpret_cast<const uint32_t *>(iota), kIota);
+    }
+  });
 }
 
 /* ------------------------------------------------------------------ C ABI ------------------- */
@@ -455,6 +574,16 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->rows_per_byte = h->nnz_per_byte = 0.0;
   h->launches = 0;
   h->d_max = NULL;
+  h->pool = NULL;
+  h->copied_h2d = h->copied_d2h = 0;
+  {
+    /* default: a quarter of the host's cores, at most four (B200P_HOST_THREADS overrides) */
+    const unsigned hw = std::thread::hardware_concurrency();
+    int n = static_cast<int>(std::min(4u, std::max(1u, hw / 4u)));
+    const char *env = std::getenv("B200P_HOST_THREADS");
+    if (env != NULL && env[0] != '\0') n = std::atoi(env);
+    h->host_threads = std::max(0, std::min(n, 64));
+  }
   h->profiling = false;
   for (int k = 0; k < 3; ++k) { h->kernel_ms[k] = 0.0; h->kernel_launches[k] = 0; }
 
@@ -495,6 +624,7 @@ void b200p_destroy(b200p_handle h) {
   for (size_t i = 0; i < h->slots.size(); ++i) DestroySlot(&h->slots[i]);
   DestroySlot(&h->resident);
   cudaFree(h->d_max);
+  delete h->pool;
   delete h;
 }
 
@@ -593,6 +723,24 @@ int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t
   CUDA_TRY(h, on_device.status());
   CUDA_TRY(h, cudaMemcpyAsync(host_dst, device_src, nbytes, cudaMemcpyDeviceToHost, h->resident.stream));
   CUDA_TRY(h, cudaStreamSynchronize(h->resident.stream));
+  h->copied_d2h += nbytes;
+  return B200P_OK;
+}
+
+int b200p_set_host_threads(b200p_handle h, int threads) {
+  if (h == NULL || threads < 0 || threads > 64) return B200P_E_INVALID;
+  if (h->pool != NULL && h->pool->threads() != threads) {
+    delete h->pool;
+    h->pool = NULL;
+  }
+  h->host_threads = threads;
+  return B200P_OK;
+}
+
+int b200p_copied_bytes(b200p_handle h, uint64_t *host_to_device, uint64_t *device_to_host) {
+  if (h == NULL) return B200P_E_INVALID;
+  if (host_to_device != NULL) *host_to_device = h->copied_h2d;
+  if (device_to_host != NULL) *device_to_host = h->copied_d2h;
   return B200P_OK;
 }
 
@@ -687,6 +835,7 @@ int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes) {
   s->text = s->d_text;
   if (nbytes != 0) {
     CUDA_TRY(h, cudaMemcpyAsync(s->d_text, src, nbytes, cudaMemcpyHostToDevice, s->stream));
+    h->copied_h2d += nbytes;
   }
   const int rc = EnqueueParse(h, s);
   if (rc != B200P_OK) return rc;
@@ -718,16 +867,50 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
     const size_t iw = h->cfg.index_bytes;
     cudaStream_t st = s->stream;
     if (rows != 0) {
+      /* Wide CSV rows: index[] is fully determined by offset[] (the j-th non-label field of a row
+         has column id j, csv_parser.h:84-88), so those nnz * index_bytes bytes are not brought
+         back over PCIe -- about half of this path's device-to-host traffic -- but written by a
+         few host threads while the value[] copy is still on the link.  Rows shorter than 16
+         entries on average are cheaper to copy than to rebuild row by row. */
+      const bool rebuild = h->cfg.format == B200P_FORMAT_CSV && h->host_threads > 0 &&
+                           nnz >= 16 * rows;
+      uint64_t bytes = (rows + 1) * 8 + rows * 4;
       CUDA_TRY(h, cudaMemcpyAsync(s->host.offset, s->dev.offset, (rows + 1) * 8, cudaMemcpyDeviceToHost, st));
-      CUDA_TRY(h, cudaMemcpyAsync(s->host.label, s->dev.label, rows * 4, cudaMemcpyDeviceToHost, st));
-      if (sum.total[kWeights] != 0) CUDA_TRY(h, cudaMemcpyAsync(s->host.weight, s->dev.weight, sum.total[kWeights] * 4, cudaMemcpyDeviceToHost, st));
-      if (sum.total[kQids] != 0) CUDA_TRY(h, cudaMemcpyAsync(s->host.qid, s->dev.qid, sum.total[kQids] * 8, cudaMemcpyDeviceToHost, st));
-      if (nnz != 0) {
-        CUDA_TRY(h, cudaMemcpyAsync(s->host.index, s->dev.index, nnz * iw, cudaMemcpyDeviceToHost, st));
-        if (h->cfg.format == B200P_FORMAT_LIBFM) CUDA_TRY(h, cudaMemcpyAsync(s->host.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
+      if (rebuild) {
+        if (s->offsets_home == NULL) {
+          CUDA_TRY(h, cudaEventCreateWithFlags(&s->offsets_home, cudaEventDisableTiming));
+        }
+        CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
       }
-      if (sum.total[kValues] != 0) CUDA_TRY(h, cudaMemcpyAsync(s->host.value, s->dev.value, sum.total[kValues] * 4, cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(h, cudaMemcpyAsync(s->host.label, s->dev.label, rows * 4, cudaMemcpyDeviceToHost, st));
+      if (sum.total[kWeights] != 0) {
+        CUDA_TRY(h, cudaMemcpyAsync(s->host.weight, s->dev.weight, sum.total[kWeights] * 4, cudaMemcpyDeviceToHost, st));
+        bytes += sum.total[kWeights] * 4;
+      }
+      if (sum.total[kQids] != 0) {
+        CUDA_TRY(h, cudaMemcpyAsync(s->host.qid, s->dev.qid, sum.total[kQids] * 8, cudaMemcpyDeviceToHost, st));
+        bytes += sum.total[kQids] * 8;
+      }
+      if (nnz != 0) {
+        if (!rebuild) {
+          CUDA_TRY(h, cudaMemcpyAsync(s->host.index, s->dev.index, nnz * iw, cudaMemcpyDeviceToHost, st));
+          bytes += nnz * iw;
+        }
+        if (h->cfg.format == B200P_FORMAT_LIBFM) {
+          CUDA_TRY(h, cudaMemcpyAsync(s->host.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
+          bytes += nnz * iw;
+        }
+      }
+      if (sum.total[kValues] != 0) {
+        CUDA_TRY(h, cudaMemcpyAsync(s->host.value, s->dev.value, sum.total[kValues] * 4, cudaMemcpyDeviceToHost, st));
+        bytes += sum.total[kValues] * 4;
+      }
+      if (rebuild) {
+        CUDA_TRY(h, cudaEventSynchronize(s->offsets_home));
+        RebuildCsvIndex(h, s, rows);
+      }
       CUDA_TRY(h, cudaStreamSynchronize(st));
+      h->copied_d2h += bytes;
     }
   }
   FillBlock(h, *s, s->host, false, out);

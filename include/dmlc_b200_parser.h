@@ -129,6 +129,21 @@ int b200p_next(b200p_handle h, b200p_rowblock *out);
 int b200p_pending(b200p_handle h);
 
 /*
+ * Host threads b200p_next may use (0..64). Their one job: for CSV chunks whose rows average 16
+ * or more entries, index[] is not copied back from the GPU -- it is implied by offset[] (the j-th
+ * non-label field of a row has column id j, src/data/csv_parser.h:84-88) -- but written into the
+ * pinned result by these threads while value[] is still on the link; that halves the
+ * device-to-host bytes of the path. 0 = always copy index[] from the GPU. Default: a quarter of
+ * the host's cores, at most 4; the environment variable B200P_HOST_THREADS overrides the default.
+ * The arrays returned are identical either way. No reference counterpart.
+ */
+int b200p_set_host_threads(b200p_handle h, int threads);
+
+/* bytes this handle has moved over the host link so far: text in (b200p_submit) and arrays out
+   (b200p_next, b200p_fetch). bench.py's e2e byte counts. No reference counterpart. */
+int b200p_copied_bytes(b200p_handle h, uint64_t *host_to_device, uint64_t *device_to_host);
+
+/*
  * Largest value in index[] and field[] (0 when empty) of the block most recently returned by
  * b200p_next or b200p_parse_device[_finish] on this handle, reduced on the GPU from the arrays
  * still resident there. Replaces the per-element max_index / max_field bookkeeping of

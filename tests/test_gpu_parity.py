@@ -256,3 +256,48 @@ def test_oversize_chunk_is_refused(cuda_lib):
     with pytest.raises(RuntimeError, match="16-byte aligned"):
         p.parse_device_async(257, 64)
     p.close()
+
+
+@pytest.mark.parametrize("ib", [4, 8])
+def test_csv_column_ids_rebuilt_on_the_host(cuda_lib, oracle, ib):
+    """b200p_next leaves index[] of wide CSV rows on the GPU and writes it from offset[] with host
+    threads; the arrays must equal the oracle's for ragged rows too, with any thread count, and
+    the handle's own byte count must show the saving."""
+    rnd = random.Random(11)
+    lines = []
+    for i in range(4000):
+        width = rnd.choice([0, 1, 17, 40, 129, 300]) if i % 50 else 5000   # > the 4096-entry iota block
+        lines.append(",".join("%.4g" % rnd.uniform(-9, 9) for _ in range(width)))
+    raw = ("\n".join(lines) + "\n").encode()
+    exp = oracle.parse_buffer("csv", raw, ib, 2)
+    assert exp["error"] == 0 and len(exp["index"]) >= 16 * len(exp["label"])
+    cuts, pos = [0], 0
+    while pos < len(raw):
+        pos = min(len(raw), pos + (300 << 10))
+        if pos < len(raw):
+            pos = raw.index(b"\n", pos) + 1
+        cuts.append(pos)
+    moved = {}
+    for threads in (0, 1, 4):
+        p = _parser(cuda_lib, "csv", ib, 2, chunk_bytes=1 << 20, depth=2)
+        p.set_host_threads(threads)
+        blocks = []
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            while p.pending() >= 2:
+                blocks.append(p.next())
+            p.submit(raw[a:b])
+        while p.pending():
+            blocks.append(p.next())
+        moved[threads] = p.copied_bytes()
+        p.close()
+        got = {k: np.concatenate([b[k] for b in blocks]) for k in ("label", "weight", "qid", "field", "index", "value")}
+        offs, run = [np.zeros(1, dtype=np.uint64)], 0
+        for b in blocks:
+            offs.append(b["offset"][1:] + np.uint64(run))
+            run += len(b["index"])
+        got["offset"] = np.concatenate(offs)
+        got["error"] = 0
+        assert same_rowblocks(got, exp) is None, threads
+    assert moved[0][0] == moved[4][0] == len(raw)
+    assert moved[0][1] - moved[4][1] == ib * len(exp["index"])
+    assert moved[1] == moved[4]
