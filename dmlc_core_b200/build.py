@@ -89,7 +89,8 @@ def build_host(force=False):
     ccs = [s for s in srcs if s.endswith(".cc")]
     if not ccs:
         return None
-    if force or _stale(target, srcs + [os.path.join(ROOT, "include", "dmlc_b200_parser.h")]):
+    if force or _stale(target, srcs + [os.path.join(ROOT, "include", "dmlc_b200_parser.h"),
+                                       os.path.join(PKG, "csrc", "host_pool.h")]):
         _run(["g++", "-O2", "-std=c++14", "-fPIC", "-shared", "-pthread", "-Wall",
               "-I" + os.path.join(PKG, "include"), "-I" + os.path.join(ROOT, "include"),
               "-o", target] + ccs + ["-L" + LIB, "-ldmlc_b200", "-Wl,-rpath,$ORIGIN", "-ldl"])

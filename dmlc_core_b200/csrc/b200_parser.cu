@@ -9,6 +9,7 @@
 #include <pthread.h>
 
 #include <algorithm>
+#include <atomic>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -22,6 +23,7 @@
 #include <vector>
 
 #include "../../include/dmlc_b200_parser.h"
+#include "host_pool.h"
 #include "text_kernels.cuh"
 
 namespace b200p {
@@ -68,69 +70,6 @@ struct Slot {
   Slot() { std::memset(this, 0, sizeof(*this)); }
 };
 
-/*
- * A few host threads for the one piece of per-element host work in the library: rebuilding the
- * column ids of wide CSV rows from offset[] instead of bringing them back over PCIe (b200p_next).
- * Run(parts, fn) calls fn(0..parts-1) once each, the calling thread included, and returns when
- * all are done.
- */
-class HostPool {
- public:
-  explicit HostPool(int threads) : fn_(NULL), parts_(0), next_(0), left_(0), epoch_(0), stop_(false) {
-    for (int i = 1; i < threads; ++i) workers_.emplace_back([this] { Work(); });
-  }
-  ~HostPool() {
-    {
-      std::lock_guard<std::mutex> g(m_);
-      stop_ = true;
-    }
-    wake_.notify_all();
-    for (std::thread &t : workers_) t.join();
-  }
-  int threads() const { return static_cast<int>(workers_.size()) + 1; }
-  void Run(int parts, const std::function<void(int)> &fn) {
-    std::unique_lock<std::mutex> g(m_);
-    fn_ = &fn;
-    parts_ = parts;
-    next_ = 0;
-    left_ = parts;
-    ++epoch_;
-    wake_.notify_all();
-    Drain(&g);
-    idle_.wait(g, [this] { return left_ == 0; });
-    fn_ = NULL;
-  }
-
- private:
-  void Drain(std::unique_lock<std::mutex> *g) { /* called with the lock held */
-    while (fn_ != NULL && next_ < parts_) {
-      const int mine = next_++;
-      const std::function<void(int)> *fn = fn_;
-      g->unlock();
-      (*fn)(mine);
-      g->lock();
-      if (--left_ == 0) idle_.notify_all();
-    }
-  }
-  void Work() {
-    std::unique_lock<std::mutex> g(m_);
-    uint64_t seen = 0;
-    for (;;) {
-      wake_.wait(g, [&] { return stop_ || epoch_ != seen; });
-      if (stop_) return;
-      seen = epoch_;
-      Drain(&g);
-    }
-  }
-  std::vector<std::thread> workers_;
-  std::mutex m_;
-  std::condition_variable wake_, idle_;
-  const std::function<void(int)> *fn_;
-  int parts_, next_, left_;
-  uint64_t epoch_;
-  bool stop_;
-};
-
 /* index[offset[r] + j] = j for the rows [r0, r1): what CSVParser::ParseBlock stores as the
    column id of the j-th non-label field of a row (reference csv_parser.h:84-88) */
 template <typename T>
@@ -163,12 +102,17 @@ struct b200p_parser_s {
   int returned_slot;         /* slot whose host arrays the caller currently holds, or -1 */
   const Slot *last_block;    /* slot whose device arrays hold the block handed out last */
   double rows_per_byte, nnz_per_byte; /* densest chunk seen so far: sizes later allocations */
-  uint64_t launches;
+  std::atomic<uint64_t> launches;
+  /* Streaming path, two threads: one may feed (b200p_input_buffer / b200p_submit) while another
+     drains (b200p_next / b200p_pending / b200p_block_max).  `mu` guards the slot bookkeeping
+     (slots' busy flags, in_flight, lent_slot, returned_slot, the density estimate); it is never
+     held across a wait for a chunk in flight.  err_mu guards `error`, prof_mu one profiling bracket. */
+  std::mutex mu, err_mu, prof_mu;
   unsigned long long *d_max; /* two words for b200p_block_max, allocated on first use */
   int host_threads;          /* b200p_set_host_threads; 0 = column ids always come from the GPU */
   HostPool *pool;            /* created on first use */
   std::vector<uint64_t> iota; /* 0, 1, 2, ... in the handle's index width */
-  uint64_t copied_h2d, copied_d2h;
+  std::atomic<uint64_t> copied_h2d, copied_d2h;
   /* optional per-kernel timing (b200p_set_profiling): event pairs around each launch */
   bool profiling;
   struct Timed { int kind; cudaEvent_t start, stop; };
@@ -198,6 +142,11 @@ class DeviceScope {
   cudaError_t status_;
 };
 
+static void SetError(b200p_handle h, const char *msg) {
+  std::lock_guard<std::mutex> g(h->err_mu);
+  h->error = msg;
+}
+
 #define CUDA_TRY(h, expr)                                                              \
   do {                                                                                 \
     cudaError_t e_ = (expr);                                                           \
@@ -205,7 +154,7 @@ class DeviceScope {
       char buf_[512];                                                                  \
       std::snprintf(buf_, sizeof(buf_), "CUDA error %s at %s:%d: %s", cudaGetErrorName(e_), \
                     __FILE__, __LINE__, cudaGetErrorString(e_));                       \
-      (h)->error = buf_;                                                               \
+      SetError((h), buf_);                                                             \
       return B200P_E_CUDA;                                                             \
     }                                                                                  \
   } while (0)
@@ -213,6 +162,7 @@ class DeviceScope {
 /* profiling brackets: only active after b200p_set_profiling(h, 1) */
 static void ProfBegin(b200p_handle h, int kind, cudaStream_t s) {
   if (!h->profiling) return;
+  h->prof_mu.lock(); /* released by the matching ProfEnd: a bracket spans one launch */
   b200p_parser_s::Timed t;
   t.kind = kind;
   cudaEventCreate(&t.start);
@@ -223,8 +173,10 @@ static void ProfBegin(b200p_handle h, int kind, cudaStream_t s) {
 static void ProfEnd(b200p_handle h, cudaStream_t s) {
   if (!h->profiling) return;
   cudaEventRecord(h->timed.back().stop, s);
+  h->prof_mu.unlock();
 }
 static void ProfCollect(b200p_handle h) {
+  std::lock_guard<std::mutex> g(h->prof_mu);
   for (size_t i = 0; i < h->timed.size(); ++i) {
     float ms = 0.f;
     if (cudaEventSynchronize(h->timed[i].stop) == cudaSuccess &&
@@ -239,7 +191,7 @@ static void ProfCollect(b200p_handle h) {
 }
 
 static int Fail(b200p_handle h, int code, const char *msg) {
-  h->error = msg;
+  SetError(h, msg);
   return code;
 }
 
@@ -440,8 +392,11 @@ static int FinishParse(b200p_handle h, Slot *s) {
     if (rc2 != B200P_OK) return rc2;
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
   }
-  h->rows_per_byte = std::max(h->rows_per_byte, static_cast<double>(sum.total[kRows]) / s->nbytes);
-  h->nnz_per_byte = std::max(h->nnz_per_byte, static_cast<double>(sum.total[kNnz]) / s->nbytes);
+  {
+    std::lock_guard<std::mutex> g(h->mu);
+    h->rows_per_byte = std::max(h->rows_per_byte, static_cast<double>(sum.total[kRows]) / s->nbytes);
+    h->nnz_per_byte = std::max(h->nnz_per_byte, static_cast<double>(sum.total[kNnz]) / s->nbytes);
+  }
   if (sum.error & kErrInternal) {
     return Fail(h, B200P_E_CUDA, "internal consistency check failed (checked build): a queue or output index left its bounds");
   }
@@ -546,7 +501,11 @@ const char *b200p_version(void) { return "dmlc_b200 0.1 sm_100a"; }
 #endif
 
 const char *b200p_last_error(b200p_handle h) {
-  return h != NULL ? h->error.c_str() : g_create_error.c_str();
+  if (h == NULL) return g_create_error.c_str();
+  static thread_local std::string mine; /* a copy: the other thread may fail while this one reads */
+  std::lock_guard<std::mutex> g(h->err_mu);
+  mine = h->error;
+  return mine.c_str();
 }
 
 int b200p_create(const b200p_config *config, b200p_handle *out) {
@@ -567,6 +526,7 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   if (rb != 0u) rb = std::max<uint32_t>(kStepBytes, (rb + kStepBytes - 1) / kStepBytes * kStepBytes);
   h->range_bytes = rb;
   h->depth = config->depth > 0 ? std::min(config->depth, 8) : 3;
+  h->slots.reserve(static_cast<size_t>(h->depth) + 2);
   h->lent_slot = -1;
   h->returned_slot = -1;
   h->last_block = NULL;
@@ -628,7 +588,7 @@ void b200p_destroy(b200p_handle h) {
   delete h;
 }
 
-uint64_t b200p_launch_count(b200p_handle h) { return h != NULL ? h->launches : 0; }
+uint64_t b200p_launch_count(b200p_handle h) { return h != NULL ? h->launches.load() : 0; }
 
 int b200p_set_profiling(b200p_handle h, int on) {
   if (h == NULL) return B200P_E_INVALID;
@@ -739,8 +699,8 @@ int b200p_set_host_threads(b200p_handle h, int threads) {
 
 int b200p_copied_bytes(b200p_handle h, uint64_t *host_to_device, uint64_t *device_to_host) {
   if (h == NULL) return B200P_E_INVALID;
-  if (host_to_device != NULL) *host_to_device = h->copied_h2d;
-  if (device_to_host != NULL) *device_to_host = h->copied_d2h;
+  if (host_to_device != NULL) *host_to_device = h->copied_h2d.load();
+  if (device_to_host != NULL) *device_to_host = h->copied_d2h.load();
   return B200P_OK;
 }
 
@@ -785,6 +745,7 @@ int b200p_input_buffer(b200p_handle h, void **host_ptr, uint64_t *capacity) {
   if (h == NULL || host_ptr == NULL) return B200P_E_INVALID;
   DeviceScope on_device(h->cfg.device);
   CUDA_TRY(h, on_device.status());
+  std::lock_guard<std::mutex> g(h->mu);
   if (h->lent_slot < 0) {
     const int id = FreeSlotIndex(h);
     if (id < 0) return Fail(h, B200P_E_AGAIN, "all pipeline slots are in flight: call b200p_next");
@@ -802,6 +763,7 @@ int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes) {
   if (nbytes > B200P_MAX_CHUNK_BYTES) return Fail(h, B200P_E_INVALID, "chunk larger than B200P_MAX_CHUNK_BYTES");
   DeviceScope on_device(h->cfg.device);
   CUDA_TRY(h, on_device.status());
+  std::lock_guard<std::mutex> g(h->mu);
   int id = h->lent_slot;
   const bool in_place = id >= 0 && text == h->slots[id].h_text;
   if (id < 0) {
@@ -844,19 +806,29 @@ int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes) {
   return B200P_OK;
 }
 
-int b200p_pending(b200p_handle h) { return h != NULL ? static_cast<int>(h->in_flight.size()) : 0; }
+int b200p_pending(b200p_handle h) {
+  if (h == NULL) return 0;
+  std::lock_guard<std::mutex> g(h->mu);
+  return static_cast<int>(h->in_flight.size());
+}
 
 int b200p_next(b200p_handle h, b200p_rowblock *out) {
   if (h == NULL || out == NULL) return B200P_E_INVALID;
-  if (h->in_flight.empty()) return Fail(h, B200P_E_EMPTY, "b200p_next: nothing submitted");
   DeviceScope on_device(h->cfg.device);
   CUDA_TRY(h, on_device.status());
-  const int id = h->in_flight.front();
-  h->in_flight.pop_front();
-  Slot *s = &h->slots[id];
-  s->busy = false;
-  h->returned_slot = -1; /* the block handed out before this call is released now */
-  h->last_block = NULL;
+  Slot *s = NULL;
+  {
+    std::lock_guard<std::mutex> g(h->mu);
+    if (h->in_flight.empty()) return Fail(h, B200P_E_EMPTY, "b200p_next: nothing submitted");
+    const int id = h->in_flight.front();
+    h->in_flight.pop_front();
+    s = &h->slots[id];   /* slots never moves: reserved for depth + 2 entries at creation */
+    s->busy = false;
+    /* the block handed out before this call is released and this one is held, in one step, so
+       that a concurrent b200p_submit cannot pick the slot being finished here */
+    h->returned_slot = id;
+    h->last_block = NULL;
+  }
   int rc = FinishParse(h, s);
   if (rc != B200P_OK) return rc;
   if (s->nbytes != 0) {
@@ -914,7 +886,6 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
     }
   }
   FillBlock(h, *s, s->host, false, out);
-  h->returned_slot = id;
   h->last_block = s;
   return B200P_OK;
 }

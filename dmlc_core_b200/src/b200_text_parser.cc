@@ -3,9 +3,11 @@
  * src/data.cc:21-85 (factories, CreateParser_, Parser<I>::Create) on top of
  * TextParserBase / LibSVMParser / LibFMParser / CSVParser / ThreadedParser.
  *
- * Host side only: reads whole-line chunks of its InputSplit partition straight into the pinned
- * staging buffers of the C ABI (include/dmlc_b200_parser.h), keeps `depth` chunks in flight on
- * the GPU, and exposes each parsed chunk as one RowBlock whose arrays live in pinned host
+ * Host side only: a feeder thread reads whole-line chunks of the InputSplit partition straight
+ * into the pinned staging buffers of the C ABI (include/dmlc_b200_parser.h) and submits them,
+ * keeping `depth` chunks in flight on the GPU -- the role ThreadedInputSplit + ThreadedParser
+ * play in the reference (src/io/threaded_input_split.h:29-79, src/data/parser.h:70-126) -- while
+ * the consumer thread takes each parsed chunk as one RowBlock whose arrays live in pinned host
  * memory.  All parsing happens in the sm_100a kernels; there is no CPU fallback.
  */
 #include <dmlc/data.h>
@@ -16,11 +18,14 @@
 
 #include <algorithm>
 #include <chrono>
-#include <future>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <limits>
+#include <mutex>
+#include <thread>
 #include <vector>
 
 #include "../../include/dmlc_b200_parser.h"
@@ -65,14 +70,16 @@ static int DeviceFor(unsigned part_index) {
  *   DMLC_B200_DEVICE    CUDA device ordinal (default 0), or "auto" = part_index % DMLC_B200_NUM_DEVICES
  *   DMLC_B200_CHUNK_MB  chunk size in MiB (default 64; the reference uses 8, input_split_base.h:40)
  *   DMLC_B200_DEPTH     chunks in flight (default 3)
- *   DMLC_B200_READ_THREADS  threads of one parallel pread (default: half the cores, at most 8)
+ *   DMLC_B200_READ_THREADS  threads of one parallel pread (default: 3/4 of the cores, at most 12,
+ *                           divided by LOCAL_WORLD_SIZE)
  */
 template <typename IndexType>
 class B200TextParser : public Parser<IndexType> {
  public:
   B200TextParser(InputSplit *source, int format, int label_column, unsigned part_index = 0)
       : source_(source), text_(NULL), handle_(NULL),
-        bytes_read_(0), exhausted_(false) {
+        bytes_read_(0), exhausted_(false), feeder_running_(false), feeder_stop_(false),
+        feeder_done_(false) {
     std::memset(&block_, 0, sizeof(block_));
 #if B200_HAVE_TEXT_SPLIT
     text_ = dynamic_cast<TextSplit *>(source);
@@ -104,9 +111,7 @@ class B200TextParser : public Parser<IndexType> {
   }
 
   virtual ~B200TextParser() {
-#if B200_HAVE_TEXT_SPLIT
-    CancelRead();
-#endif
+    StopFeeder();
     b200p_destroy(handle_);
     delete source_;
   }
@@ -114,9 +119,8 @@ class B200TextParser : public Parser<IndexType> {
   virtual void BeforeFirst(void) {
     /* discard what is still in flight, then rewind the source (reference text_parser.h:40-42;
        like there, BytesRead keeps counting across passes) */
-#if B200_HAVE_TEXT_SPLIT
-    CancelRead();
-#endif
+    StopFeeder();
+    feeder_error_ = nullptr;
     b200p_rowblock dropped;
     while (b200p_pending(handle_) > 0) {
       if (b200p_next(handle_, &dropped) != B200P_OK) break;
@@ -127,10 +131,19 @@ class B200TextParser : public Parser<IndexType> {
 
   virtual bool Next(void) {
     for (;;) {
-      Feed();
-      if (b200p_pending(handle_) == 0) return false;
+      if (text_ != NULL) {
+        if (!WaitForFeeder()) return false;
+      } else {
+        Feed();
+        if (b200p_pending(handle_) == 0) return false;
+      }
       b200p_rowblock b;
-      Check(b200p_next(handle_, &b));
+      const int rc = b200p_next(handle_, &b);
+      if (text_ != NULL) {   /* a pipeline slot came free */
+        { std::lock_guard<std::mutex> g(feeder_mu_); }
+        feeder_cv_.notify_all();
+      }
+      Check(rc);
       bytes_read_ += b.text_bytes;
       if (b.rows == 0) continue;  /* chunks without rows are skipped (reference parser.h:33-38) */
       block_.size = static_cast<size_t>(b.rows);
@@ -159,99 +172,128 @@ class B200TextParser : public Parser<IndexType> {
   }
 
  private:
-  /* keep the pipeline full: read chunks and enqueue them until `depth` are in flight */
-  void Feed() {
-    while ((!exhausted_ || !backlog_.empty()) && b200p_pending(handle_) < depth_) {
+  /*
+   * TextSplit sources.  The feeder thread loops { borrow the pinned staging buffer of a free
+   * pipeline slot; fill it with the next whole lines of the partition (parallel pread);
+   * b200p_submit } whenever fewer than `depth` chunks are in flight; the consumer thread only
+   * calls b200p_next.  The C ABI allows exactly this pairing of threads on one handle.  An
+   * exception in the feeder (I/O error) is kept and rethrown by Next() once the blocks submitted
+   * before it have been delivered, like ThreadedIter does (include/dmlc/threadediter.h:456-466).
+   */
+  void FeederLoop() {
 #if B200_HAVE_TEXT_SPLIT
-      if (text_ != NULL) {
-        /* Read-ahead: the next chunk is read (parallel pread, straight into the pinned staging
-           buffer of a free pipeline slot) by a background task while this thread waits for the
-           GPU in b200p_next and while the consumer works on the block it was handed. The task
-           only fills memory; every call into the C ABI stays on the consumer thread. */
-        if (!read_ahead_.valid() && !StartRead()) break;   /* no staging buffer free right now */
-        if (b200p_pending(handle_) > 0 &&
-            read_ahead_.wait_for(std::chrono::seconds(0)) != std::future_status::ready) {
-          break;                                     /* results are waiting: let the read run */
+    try {
+      for (;;) {
+        {
+          std::unique_lock<std::mutex> g(feeder_mu_);
+          feeder_cv_.wait(g, [this] { return feeder_stop_ || b200p_pending(handle_) < depth_; });
+          if (feeder_stop_) break;
         }
-        size_t n = read_ahead_.get();                /* rethrows a dmlc::Error of the reader */
-        void *pinned = read_buffer_;
+        void *pinned = NULL;
+        uint64_t cap = 0;
+        const int rc = b200p_input_buffer(handle_, &pinned, &cap);
+        if (rc == B200P_E_AGAIN) {   /* every slot taken: wait for the consumer to return one */
+          std::unique_lock<std::mutex> g(feeder_mu_);
+          feeder_cv_.wait_for(g, std::chrono::milliseconds(1));
+          continue;
+        }
+        Check(rc);
+        size_t n = text_->ReadLines(pinned, static_cast<size_t>(cap));
+        const void *chunk = pinned;
         if (n == TextSplit::kLineTooLong) {
           /* a single line longer than the staging buffer: read it through a growing heap
              buffer; b200p_submit then enlarges the slot */
-          size_t big = read_capacity_;
+          size_t big = static_cast<size_t>(cap);
           do {
             big *= 2;
             CHECK(big <= B200P_MAX_CHUNK_BYTES) << "a single line exceeds " << B200P_MAX_CHUNK_BYTES << " bytes";
             spill_.resize(big);
             n = text_->ReadLines(spill_.data(), big);
           } while (n == TextSplit::kLineTooLong);
-          pinned = spill_.data();
+          chunk = spill_.data();
         }
-        if (n == 0) {
-          /* end of the partition: an empty chunk hands the borrowed staging buffer back
-             (it comes out of b200p_next as a block without rows, which Next() skips) */
-          exhausted_ = true;
-          Check(b200p_submit(handle_, read_buffer_, 0));
-          break;
-        }
-        Check(b200p_submit(handle_, pinned, n));
-        continue;
+        /* at the end of the partition an empty chunk hands the borrowed buffer back (it comes
+           out of b200p_next as a block without rows, which Next() skips) */
+        Check(b200p_submit(handle_, n == 0 ? pinned : chunk, n));
+        { std::lock_guard<std::mutex> g(feeder_mu_); }
+        feeder_cv_.notify_all();
+        if (n == 0) break;
       }
-#endif
-      {
-        /* any other InputSplit: its chunks are copied into the staging buffer by b200p_submit
-           (the Blob dies at the next NextChunk); oversized chunks are cut at line ends */
-        if (!backlog_.empty()) {
-          Check(b200p_submit(handle_, backlog_.front().data(), backlog_.front().size()));
-          backlog_.erase(backlog_.begin());
-          continue;
-        }
-        InputSplit::Blob chunk;
-        if (!source_->NextChunk(&chunk)) { exhausted_ = true; break; }
-        const char *base = static_cast<const char *>(chunk.dptr);
-        if (chunk.size <= B200P_MAX_CHUNK_BYTES) {
-          Check(b200p_submit(handle_, base, chunk.size));
-          continue;
-        }
-        size_t done = 0;
-        while (done < chunk.size) {
-          size_t n = std::min<size_t>(chunk.size - done, B200P_MAX_CHUNK_BYTES);
-          if (done + n < chunk.size) {
-            while (n > 1 && base[done + n - 1] != '\n' && base[done + n - 1] != '\r') --n;
-          }
-          backlog_.push_back(std::string(base + done, n));
-          done += n;
-        }
-      }
+    } catch (...) {
+      feeder_error_ = std::current_exception();
     }
-#if B200_HAVE_TEXT_SPLIT
-    /* pipeline full: still start reading the chunk after it */
-    if (text_ != NULL && !exhausted_ && !read_ahead_.valid()) StartRead();
 #endif
+    {
+      std::lock_guard<std::mutex> g(feeder_mu_);
+      feeder_done_ = true;
+    }
+    feeder_cv_.notify_all();
   }
 
-#if B200_HAVE_TEXT_SPLIT
-  bool StartRead() {
-    void *pinned = NULL;
-    uint64_t cap = 0;
-    const int rc = b200p_input_buffer(handle_, &pinned, &cap);
-    if (rc == B200P_E_AGAIN) return false;
-    Check(rc);
-    read_buffer_ = pinned;
-    read_capacity_ = static_cast<size_t>(cap);
-    TextSplit *split = text_;
-    read_ahead_ = std::async(std::launch::async, [split, pinned, cap]() {
-      return split->ReadLines(pinned, static_cast<size_t>(cap));
-    });
-    return true;
+  /* consumer side: true when a chunk is in flight, false at the end of the partition */
+  bool WaitForFeeder() {
+    if (!feeder_running_ && !exhausted_) {
+      feeder_stop_ = false;
+      feeder_done_ = false;
+      feeder_running_ = true;
+      feeder_ = std::thread([this] { FeederLoop(); });
+    }
+    if (feeder_running_) {
+      std::unique_lock<std::mutex> g(feeder_mu_);
+      feeder_cv_.wait(g, [this] { return feeder_done_ || b200p_pending(handle_) > 0; });
+    }
+    if (b200p_pending(handle_) > 0) return true;
+    /* the feeder has finished and everything it submitted has been delivered */
+    StopFeeder();
+    exhausted_ = true;
+    if (feeder_error_) {
+      std::exception_ptr e = feeder_error_;
+      feeder_error_ = nullptr;
+      std::rethrow_exception(e);
+    }
+    return false;
   }
-  void CancelRead() {
-    if (read_ahead_.valid()) {
-      try { read_ahead_.get(); } catch (...) {}
-      b200p_submit(handle_, read_buffer_, 0);   /* returns the borrowed staging buffer */
+
+  void StopFeeder() {
+    if (!feeder_running_) return;
+    {
+      std::lock_guard<std::mutex> g(feeder_mu_);
+      feeder_stop_ = true;
+    }
+    feeder_cv_.notify_all();
+    feeder_.join();
+    feeder_running_ = false;
+  }
+
+  /* any other InputSplit (the build against the reference's own headers): chunks are copied into
+     the staging buffer by b200p_submit on the consumer thread (the Blob dies at the next
+     NextChunk); oversized chunks are cut at line ends */
+  void Feed() {
+    while ((!exhausted_ || !backlog_.empty()) && b200p_pending(handle_) < depth_) {
+      if (!backlog_.empty()) {
+        Check(b200p_submit(handle_, backlog_.front().data(), backlog_.front().size()));
+        backlog_.erase(backlog_.begin());
+        continue;
+      }
+      InputSplit::Blob chunk;
+      if (!source_->NextChunk(&chunk)) { exhausted_ = true; break; }
+      const char *base = static_cast<const char *>(chunk.dptr);
+      if (chunk.size <= B200P_MAX_CHUNK_BYTES) {
+        Check(b200p_submit(handle_, base, chunk.size));
+        continue;
+      }
+      size_t done = 0;
+      while (done < chunk.size) {
+        size_t n = std::min<size_t>(chunk.size - done, B200P_MAX_CHUNK_BYTES);
+        if (done + n < chunk.size) {
+          while (n > 1 && base[done + n - 1] != '\n' && base[done + n - 1] != '\r') --n;
+        }
+        backlog_.push_back(std::string(base + done, n));
+        done += n;
+      }
     }
   }
-#endif
+
   void Check(int rc) {
     if (rc == B200P_OK) return;
     /* B200P_E_PARSE carries the reference's CHECK text; everything surfaces as dmlc::Error */
@@ -272,11 +314,13 @@ class B200TextParser : public Parser<IndexType> {
   bool exhausted_;
   std::vector<char> spill_;
   std::vector<std::string> backlog_;
-#if B200_HAVE_TEXT_SPLIT
-  std::future<size_t> read_ahead_;   /* bytes the background read produced */
-  void *read_buffer_;
-  size_t read_capacity_;
-#endif
+  /* feeder thread (TextSplit sources) */
+  std::thread feeder_;
+  std::mutex feeder_mu_;
+  std::condition_variable feeder_cv_;
+  bool feeder_running_;   /* consumer thread only */
+  bool feeder_stop_, feeder_done_;   /* under feeder_mu_ */
+  std::exception_ptr feeder_error_;  /* written by the feeder before feeder_done_, read after */
 };
 
 /* ---- factories: same signatures and argument handling as reference src/data.cc:21-60 ---- */

@@ -7,10 +7,12 @@
 
 #include <algorithm>
 #include <cerrno>
+#include <cstdlib>
 #include <cstring>
 #include <regex>
 #include <thread>
 
+#include "../csrc/host_pool.h"
 #include "./uri_spec.h"
 
 namespace dmlc {
@@ -32,10 +34,15 @@ std::string StripTrailingSlash(std::string s) {
 }  // namespace
 
 TextSplit::TextSplit(const char *uri, unsigned part_index, unsigned num_parts)
-    : begin_(0), end_(0), cur_(0), read_threads_(1), chunk_size_hint_(8u << 20),
+    : begin_(0), end_(0), cur_(0), read_threads_(1), pool_(NULL), chunk_size_hint_(8u << 20),
       rec_pos_(0), rec_end_(0) {
+  /* three quarters of the cores, at most 12 (measured on a 16-core B200 host: one 64 MiB chunk
+     from the page cache at 39 GB/s with 8 readers, 48 GB/s with 12), shared fairly when several
+     ranks run on one host (torchrun exports LOCAL_WORLD_SIZE) */
   unsigned hw = std::thread::hardware_concurrency();
-  read_threads_ = hw >= 16 ? 8 : (hw >= 4 ? static_cast<int>(hw / 2) : 1);
+  const char *local = std::getenv("LOCAL_WORLD_SIZE");
+  const unsigned ranks = (local != NULL && std::atoi(local) > 0) ? static_cast<unsigned>(std::atoi(local)) : 1u;
+  read_threads_ = static_cast<int>(std::max(1u, std::min(12u, hw * 3u / 4u / ranks)));
   ExpandUri(uri);
   CHECK_NE(files_.size(), 0U) << "Cannot find any files that matches the URI pattern " << uri;
   start_.resize(files_.size() + 1);
@@ -45,6 +52,7 @@ TextSplit::TextSplit(const char *uri, unsigned part_index, unsigned num_parts)
 }
 
 TextSplit::~TextSplit() {
+  delete pool_;
   for (size_t i = 0; i < files_.size(); ++i) {
     if (files_[i].fd >= 0) close(files_[i].fd);
   }
@@ -191,27 +199,29 @@ void TextSplit::ReadRangeSerial(uint64_t offset, char *dst, size_t n) {
 }
 
 void TextSplit::ReadRange(uint64_t offset, char *dst, size_t n) {
-  const size_t kMinPiece = 4u << 20;
-  int pieces = static_cast<int>(std::min<size_t>(read_threads_, (n + kMinPiece - 1) / kMinPiece));
-  if (pieces <= 1) {
+  const size_t kMinPiece = 2u << 20;
+  const int pieces = static_cast<int>(std::min<size_t>(4 * static_cast<size_t>(read_threads_),
+                                                       (n + kMinPiece - 1) / kMinPiece));
+  if (pieces <= 1 || read_threads_ <= 1) {
     ReadRangeSerial(offset, dst, n);
     return;
   }
-  const size_t per = ((n + pieces - 1) / pieces + 4095) / 4096 * 4096;
-  std::vector<std::thread> pool;
-  std::vector<std::string> errors(pieces);
-  for (int i = 0; i < pieces; ++i) {
-    const size_t lo = std::min(n, per * i), hi = std::min(n, per * (i + 1));
-    if (lo == hi) continue;
-    pool.push_back(std::thread([this, offset, dst, lo, hi, i, &errors]() {
-      try {
-        ReadRangeSerial(offset + lo, dst + lo, hi - lo);
-      } catch (const dmlc::Error &e) {
-        errors[i] = e.what();
-      }
-    }));
+  /* persistent readers: spawning a dozen threads per 64 MiB chunk costs a fifth of the read */
+  if (pool_ == NULL || pool_->threads() != read_threads_) {
+    delete pool_;
+    pool_ = new b200p::HostPool(read_threads_);
   }
-  for (size_t i = 0; i < pool.size(); ++i) pool[i].join();
+  const size_t per = ((n + pieces - 1) / pieces + 4095) / 4096 * 4096;
+  std::vector<std::string> errors(pieces);
+  pool_->Run(pieces, [&](int i) {
+    const size_t lo = std::min(n, per * i), hi = std::min(n, per * (i + 1));
+    if (lo == hi) return;
+    try {
+      ReadRangeSerial(offset + lo, dst + lo, hi - lo);
+    } catch (const dmlc::Error &e) {
+      errors[i] = e.what();
+    }
+  });
   for (int i = 0; i < pieces; ++i) {
     if (!errors[i].empty()) LOG(FATAL) << errors[i];
   }

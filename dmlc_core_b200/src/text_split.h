@@ -22,6 +22,10 @@
 #include <string>
 #include <vector>
 
+namespace b200p {
+class HostPool;
+}
+
 namespace dmlc {
 namespace b200 {
 
@@ -69,6 +73,7 @@ class TextSplit : public InputSplit {
   std::vector<uint64_t> start_;   /* start_[i] = stream offset of file i; start_[n] = T */
   uint64_t begin_, end_, cur_;
   int read_threads_;
+  b200p::HostPool *pool_;   /* readers of ReadRange, created on first use */
   /* NextChunk / NextRecord state */
   std::vector<char> chunk_;
   size_t chunk_size_hint_;

@@ -121,6 +121,12 @@ int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out);
  *   b200p_next          wait for the oldest submitted chunk; pointers are pinned host memory,
  *                       valid until the next b200p_next / b200p_destroy on this handle.
  * Replaces: ParserImpl::ParseNext -> FillData (src/data/parser.h:30-44, text_parser.h:93-134).
+ *
+ * Threads: a handle may be driven by two threads at once -- one feeding (b200p_input_buffer,
+ * b200p_submit) and one draining (b200p_next, b200p_pending, b200p_block_max, b200p_last_error)
+ * -- which is how the C++ Parser keeps reading files while the consumer holds a block (the
+ * reference's ThreadedInputSplit / ThreadedParser pairing). Anything beyond that pairing, and
+ * every other entry point, needs the caller's own serialisation.
  */
 int b200p_input_buffer(b200p_handle h, void **host_ptr, uint64_t *capacity);
 int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes);
