@@ -211,3 +211,28 @@ def test_two_parsers_interleaved_in_one_process(hostapi, oracle, tmp_path, monke
         got = hostapi.concat_blocks(blocks[k], 8)
         assert same_rowblocks(got, exp) is None, k
         parsers[k].close()
+
+
+def test_rewind_and_destroy_while_the_feeder_is_running(hostapi, oracle, tmp_path, monkeypatch):
+    """BeforeFirst() and delete in the middle of a pass: the feeder thread is stopped with chunks
+    in flight and a read under way, what was in flight is dropped, and the next pass starts from
+    the first row again (reference text_parser.h:40-42 / threadediter.h BeforeFirst semantics)."""
+    from dmlc_core_b200 import datagen
+    monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
+    data, rows = datagen.generate("libsvm", 31, 12 << 20)
+    f = tmp_path / "big.svm"
+    f.write_bytes(data.tobytes())
+    exp = oracle.parse_files("libsvm", [str(f)], 0, 1, 4)
+    p = hostapi.CppParser(str(f), 0, 1, "libsvm", 4)
+    for taken in (0, 1, 3, 5):
+        for _ in range(taken):
+            assert p.next() is not None
+        p.before_first()
+    got, nblocks = p.drain()
+    assert nblocks >= 8 and same_rowblocks(got, exp) is None
+    assert p.next() is None and p.next() is None      # stays at the end
+    p.before_first()
+    assert p.next() is not None
+    p.close()                                         # destroyed mid-pass
+    for _ in range(3):                                # created and dropped without a single Next()
+        hostapi.CppParser(str(f), 0, 1, "libsvm", 4).close()

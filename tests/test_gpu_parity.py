@@ -2,6 +2,7 @@
 (oracle/dmlc_oracle.c) and the committed golden RowBlocks of the unmodified reference.
 Bit-exact for every array; floats are compared as IEEE bit patterns (tolerance: 0 ulp)."""
 import random
+import time
 
 import numpy as np
 import pytest
@@ -301,3 +302,57 @@ def test_csv_column_ids_rebuilt_on_the_host(cuda_lib, oracle, ib):
     assert moved[0][0] == moved[4][0] == len(raw)
     assert moved[0][1] - moved[4][1] == ib * len(exp["index"])
     assert moved[1] == moved[4]
+
+
+def test_one_feeding_and_one_draining_thread(cuda_lib, oracle):
+    """The threading contract of the streaming entry points (include/dmlc_b200_parser.h): one
+    thread calls b200p_input_buffer / b200p_submit while another calls b200p_next.  ctypes drops
+    the GIL inside the calls, so the two really overlap."""
+    import ctypes
+    import threading
+    from dmlc_core_b200 import datagen
+    data, rows = datagen.generate("csv", 17, 24 << 20)
+    raw = data.tobytes()
+    exp = oracle.parse_buffer("csv", raw, 4, 0)
+    cuts, pos = [0], 0
+    while pos < len(raw):
+        pos = min(len(raw), pos + (700 << 10))
+        if pos < len(raw):
+            pos = raw.index(b"\n", pos) + 1
+        cuts.append(pos)
+    chunks = [raw[a:b] for a, b in zip(cuts[:-1], cuts[1:])]
+    depth = 3
+    p = _parser(cuda_lib, "csv", 4, 0, chunk_bytes=1 << 20, depth=depth)
+    failures = []
+
+    def feed():
+        try:
+            for c in chunks:
+                while p.pending() >= depth:
+                    time.sleep(0)
+                ptr, cap = p.input_buffer()
+                assert cap >= len(c)
+                ctypes.memmove(ptr, c, len(c))
+                p.submit_in_place(ptr, len(c))
+        except Exception as e:   # surfaced by the main thread
+            failures.append(e)
+
+    t = threading.Thread(target=feed)
+    t.start()
+    blocks = []
+    while len(blocks) < len(chunks) and not failures:
+        if p.pending() == 0:
+            time.sleep(0)
+            continue
+        blocks.append(p.next())
+    t.join()
+    p.close()
+    assert not failures, failures
+    got = {k: np.concatenate([b[k] for b in blocks]) for k in ("label", "weight", "qid", "field", "index", "value")}
+    offs, run = [np.zeros(1, dtype=np.uint64)], 0
+    for b in blocks:
+        offs.append(b["offset"][1:] + np.uint64(run))
+        run += len(b["index"])
+    got["offset"] = np.concatenate(offs)
+    got["error"] = 0
+    assert same_rowblocks(got, exp) is None
