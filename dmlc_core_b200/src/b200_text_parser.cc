@@ -28,7 +28,10 @@
 #include <thread>
 #include <vector>
 
+#include <sys/mman.h>
+
 #include "../../include/dmlc_b200_parser.h"
+#include "../csrc/host_pool.h"
 #include "./uri_spec.h"
 /*
  * DMLC_B200 is defined by this package's own <dmlc/base.h>.  Built against the reference's
@@ -169,6 +172,13 @@ class B200TextParser : public Parser<IndexType> {
     uint64_t mi = 0, mf = 0;
     BlockMax(&mi, &mf);
     return mi;
+  }
+  /* text bytes of this parser's partition when the source can tell (TextSplit), else 0 */
+  size_t PartitionBytes() const {
+#if B200_HAVE_TEXT_SPLIT
+    if (text_ != NULL) return static_cast<size_t>(text_->PartitionEnd() - text_->PartitionBegin());
+#endif
+    return 0;
   }
 
  private:
@@ -384,42 +394,120 @@ Parser<IndexType> *CreateParserImpl(const char *uri, unsigned part_index, unsign
 }
 
 /*
+ * Growable array for the in-memory iterator: 2 MiB-aligned and advised for transparent huge
+ * pages (a multi-GB std::vector spends most of its append time in 4 KiB first-touch faults),
+ * grown geometrically unless Reserve was told the final size.
+ */
+template <typename T>
+class HugeArray {
+ public:
+  HugeArray() : p_(NULL), n_(0), cap_(0) {}
+  ~HugeArray() { std::free(p_); }
+  size_t size() const { return n_; }
+  bool empty() const { return n_ == 0; }
+  const T *data() const { return n_ != 0 ? p_ : NULL; }   /* NULL when empty, like BeginPtr */
+  const T &back() const { return p_[n_ - 1]; }
+  void Reserve(size_t cap) {
+    if (cap <= cap_) return;
+    const size_t kAlign = 2u << 20;
+    const size_t bytes = (cap * sizeof(T) + kAlign - 1) / kAlign * kAlign;
+    void *q = NULL;
+    CHECK(posix_memalign(&q, kAlign, bytes) == 0) << "out of memory growing a RowBlock array";
+#ifdef MADV_HUGEPAGE
+    madvise(q, bytes, MADV_HUGEPAGE);
+#endif
+    if (n_ != 0) std::memcpy(q, p_, n_ * sizeof(T));
+    std::free(p_);
+    p_ = static_cast<T *>(q);
+    cap_ = bytes / sizeof(T);
+  }
+  /* room for k more elements; returns where they go */
+  T *Extend(size_t k) {
+    if (n_ + k > cap_) Reserve(std::max(n_ + k, cap_ + cap_ / 2));
+    T *at = p_ + n_;
+    n_ += k;
+    return at;
+  }
+  void push_back(const T &v) { *Extend(1) = v; }
+
+ private:
+  T *p_;
+  size_t n_, cap_;
+  HugeArray(const HugeArray &);
+  void operator=(const HugeArray &);
+};
+
+/*
  * RowBlockIter back-end: everything in host memory (reference BasicRowIter,
  * src/data/basic_row_iter.h:62-82, with RowBlockContainer::Push, row_block.h:122-166).
+ * The parser's feeder thread and the GPU keep running while this thread appends a block, so the
+ * load is bound by how fast blocks are copied: the arrays are sized from the first block's
+ * density and the partition's byte length (one allocation, huge pages), and a block is copied
+ * in by a small pool.
  */
 template <typename IndexType>
 class InMemoryRowIter : public RowBlockIter<IndexType> {
  public:
-  explicit InMemoryRowIter(Parser<IndexType> *parser) : at_head_(true), max_index_(0) {
+  explicit InMemoryRowIter(Parser<IndexType> *parser) : at_head_(true), max_index_(0), pool_(NULL) {
     offset_.push_back(0);
     const double t0 = GetTime();
     /* the B200 parser reduces each block's largest index on the GPU, where the array still
        sits; any other parser gets the reference's per-element scan */
     B200TextParser<IndexType> *gpu = dynamic_cast<B200TextParser<IndexType> *>(parser);
+    const size_t total_bytes = gpu != NULL ? gpu->PartitionBytes() : 0;
     try {
-      while (parser->Next()) {
-        if (gpu != NULL) {
-          Append(parser->Value(), false);
-          max_index_ = std::max(max_index_, static_cast<IndexType>(gpu->BlockMaxIndex()));
-        } else {
-          Append(parser->Value(), true);
+      bool first = true;
+      double t_next = 0, t_append = 0, t_max = 0;   /* DMLC_B200_ITER_TRACE: where the load went */
+      for (;;) {
+        double ta = GetTime();
+        if (!parser->Next()) break;
+        t_next += GetTime() - ta;
+        ta = GetTime();
+        const RowBlock<IndexType> &b = parser->Value();
+        if (first && total_bytes != 0 && parser->BytesRead() != 0) {
+          /* size everything once: this block's rows and entries per text byte, plus 5 % */
+          const double scale = 1.05 * static_cast<double>(total_bytes) / parser->BytesRead();
+          const size_t rows = static_cast<size_t>(b.size * scale) + 1024;
+          const size_t nnz = static_cast<size_t>((b.offset[b.size] - b.offset[0]) * scale) + 1024;
+          offset_.Reserve(rows + 1);
+          label_.Reserve(rows);
+          if (b.weight != NULL) weight_.Reserve(rows);
+          if (b.qid != NULL) qid_.Reserve(rows);
+          if (b.field != NULL) field_.Reserve(nnz);
+          index_.Reserve(nnz);
+          if (b.value != NULL) value_.Reserve(nnz);
         }
+        first = false;
+        Append(b, gpu == NULL);
+        t_append += GetTime() - ta;
+        ta = GetTime();
+        if (gpu != NULL) {
+          max_index_ = std::max(max_index_, static_cast<IndexType>(gpu->BlockMaxIndex()));
+        }
+        t_max += GetTime() - ta;
+      }
+      if (std::getenv("DMLC_B200_ITER_TRACE") != NULL) {
+        std::fprintf(stderr, "iter trace: waiting for blocks %.3f s, appending %.3f s, max index %.3f s\n",
+                     t_next, t_append, t_max);
       }
     } catch (...) {
+      delete pool_;
       delete parser;
       throw;
     }
+    delete pool_;
+    pool_ = NULL;
     const double dt = GetTime() - t0;
     LOG(INFO) << "finish reading at " << (parser->BytesRead() >> 20UL) / (dt > 0 ? dt : 1e-9) << " MB/sec";
     delete parser;
     block_.size = label_.size();
-    block_.offset = BeginPtr(offset_);
-    block_.label = BeginPtr(label_);
-    block_.weight = BeginPtr(weight_);
-    block_.qid = BeginPtr(qid_);
-    block_.field = BeginPtr(field_);
-    block_.index = BeginPtr(index_);
-    block_.value = BeginPtr(value_);
+    block_.offset = offset_.data();
+    block_.label = label_.data();
+    block_.weight = weight_.data();
+    block_.qid = qid_.data();
+    block_.field = field_.data();
+    block_.index = index_.data();
+    block_.value = value_.data();
     /* same consistency rules as RowBlockContainer::GetBlock (row_block.h:173-177) */
     CHECK_EQ(offset_.back(), index_.size());
     CHECK(offset_.back() == value_.size() || value_.size() == 0);
@@ -434,26 +522,56 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
   virtual size_t NumCol(void) const { return static_cast<size_t>(max_index_) + 1; }
 
  private:
+  struct Piece {
+    void *dst;
+    const void *src;
+    size_t bytes;
+  };
+  template <typename T>
+  void Plan(HugeArray<T> *to, const T *from, size_t count, std::vector<Piece> *plan) {
+    if (from == NULL || count == 0) return;
+    char *dst = reinterpret_cast<char *>(to->Extend(count));
+    const char *src = reinterpret_cast<const char *>(from);
+    const size_t kPiece = 4u << 20;
+    for (size_t done = 0, bytes = count * sizeof(T); done < bytes; done += kPiece) {
+      const Piece p = {dst + done, src + done, std::min(kPiece, bytes - done)};
+      plan->push_back(p);
+    }
+  }
   void Append(const RowBlock<IndexType> &b, bool scan_max) {
     const size_t base = b.offset[0], nnz = b.offset[b.size] - base, shift = offset_.back();
-    label_.insert(label_.end(), b.label, b.label + b.size);
-    if (b.weight != NULL) weight_.insert(weight_.end(), b.weight, b.weight + b.size);
-    if (b.qid != NULL) qid_.insert(qid_.end(), b.qid, b.qid + b.size);
-    if (b.field != NULL) field_.insert(field_.end(), b.field + base, b.field + base + nnz);
-    index_.insert(index_.end(), b.index + base, b.index + base + nnz);
+    std::vector<Piece> plan;
+    Plan(&label_, b.label, b.size, &plan);
+    Plan(&weight_, b.weight, b.size, &plan);
+    Plan(&qid_, b.qid, b.size, &plan);
+    Plan(&field_, b.field != NULL ? b.field + base : NULL, nnz, &plan);
+    Plan(&index_, b.index != NULL ? b.index + base : NULL, nnz, &plan);
+    Plan(&value_, b.value != NULL ? b.value + base : NULL, nnz, &plan);
+    size_t *rebased = offset_.Extend(b.size);
+    if (plan.size() > 1) {
+      if (pool_ == NULL) {
+        const unsigned hw = std::thread::hardware_concurrency();
+        pool_ = new b200p::HostPool(static_cast<int>(std::max(1u, std::min(4u, hw / 4u))));
+      }
+      pool_->Run(static_cast<int>(plan.size()), [&plan](int i) {
+        std::memcpy(plan[i].dst, plan[i].src, plan[i].bytes);
+      });
+    } else if (plan.size() == 1) {
+      std::memcpy(plan[0].dst, plan[0].src, plan[0].bytes);
+    }
+    for (size_t i = 1; i <= b.size; ++i) rebased[i - 1] = shift + b.offset[i] - base;
     if (scan_max) {
       for (size_t i = 0; i < nnz; ++i) max_index_ = std::max(max_index_, b.index[base + i]);
     }
-    if (b.value != NULL) value_.insert(value_.end(), b.value + base, b.value + base + nnz);
-    for (size_t i = 1; i <= b.size; ++i) offset_.push_back(shift + b.offset[i] - base);
   }
   bool at_head_;
   IndexType max_index_;
   RowBlock<IndexType> block_;
-  std::vector<size_t> offset_;
-  std::vector<real_t> label_, weight_, value_;
-  std::vector<uint64_t> qid_;
-  std::vector<IndexType> field_, index_;
+  b200p::HostPool *pool_;   /* only while loading */
+  HugeArray<size_t> offset_;
+  HugeArray<real_t> label_, weight_, value_;
+  HugeArray<uint64_t> qid_;
+  HugeArray<IndexType> field_, index_;
 };
 
 /*
@@ -614,22 +732,24 @@ class CachedRowIter : public RowBlockIter<IndexType> {
   std::vector<IndexType> field_, index_;
 };
 
-/* reference CreateIter_, src/data.cc:87-107: "#cachefile" selects the disk-backed iterator */
+/* reference CreateIter_, src/data.cc:87-107: "#cachefile" selects the disk-backed iterator.
+   Like there (:95-97), the parser is created from spec.uri -- the URI without its "?key=value"
+   part -- so arguments such as format= or label_column= reach the parser only through
+   Parser::Create, never through RowBlockIter::Create (with type "auto" the iterator therefore
+   always parses LibSVM, and a CSV iterator has no label column). */
 template <typename IndexType>
 RowBlockIter<IndexType> *CreateIterImpl(const char *uri, unsigned part_index, unsigned num_parts,
                                         const char *type) {
   UriSpec spec(uri, part_index, num_parts);
-  std::string no_cache = uri;   /* the ?args travel on to the parser factory */
-  const size_t hash = no_cache.find('#');
-  if (hash != std::string::npos) no_cache.resize(hash);
   if (!spec.cache_file.empty()) {
     if (CachedRowIter<IndexType>::Usable(spec.cache_file)) {
       return new CachedRowIter<IndexType>(NULL, spec.cache_file);  /* later epochs skip parsing */
     }
     return new CachedRowIter<IndexType>(
-        CreateParserImpl<IndexType>(no_cache.c_str(), part_index, num_parts, type), spec.cache_file);
+        CreateParserImpl<IndexType>(spec.uri.c_str(), part_index, num_parts, type), spec.cache_file);
   }
-  return new InMemoryRowIter<IndexType>(CreateParserImpl<IndexType>(no_cache.c_str(), part_index, num_parts, type));
+  return new InMemoryRowIter<IndexType>(
+      CreateParserImpl<IndexType>(spec.uri.c_str(), part_index, num_parts, type));
 }
 
 }  // namespace b200

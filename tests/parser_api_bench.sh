@@ -1,7 +1,7 @@
 #!/bin/bash
 # Throughput of the C++ drop-in API (dmlc::Parser<unsigned>::Create -> Next loop) from files in
 # the page cache, next to the compiled reference when oracle/_ref travelled along.
-# Run on the GPU box from the repo root:  bash tools/parser_api_bench.sh [csv_copies] [svm_copies]
+# Run on the GPU box from the repo root:  bash tests/parser_api_bench.sh [csv_copies] [svm_copies]
 set -e
 cd "$(dirname "$0")/.."
 python tools/mkdata.py csv /dev/shm/b200_a.csv 512 "${1:-8}"

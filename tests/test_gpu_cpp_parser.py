@@ -2,6 +2,7 @@
 type) -> Next()/Value() over files, against the golden RowBlocks the unmodified reference
 produced through the same call, and against the reference itself when oracle/_ref travelled."""
 import os
+import random
 
 import numpy as np
 import pytest
@@ -165,7 +166,9 @@ def test_disk_cache_round_trip_with_the_reference(hostapi, reference, oracle, tm
     cache without parsing."""
     from dmlc_core_b200 import datagen
     monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
-    for kind, fmt, ib, lc in (("libsvm", "libsvm", 4, -1), ("libfm", "libfm", 8, -1), ("csv", "csv", 4, 0)):
+    # csv: label_column=0 in the URI does not reach the parser through RowBlockIter::Create
+    # (reference src/data.cc:95-97), so the expectation is "no label column"
+    for kind, fmt, ib, lc in (("libsvm", "libsvm", 4, -1), ("libfm", "libfm", 8, -1), ("csv", "csv", 4, -1)):
         data, rows = datagen.generate(kind, 15, 3 << 20)
         f = tmp_path / (kind + ".txt")
         f.write_bytes(data.tobytes())
@@ -236,3 +239,31 @@ def test_rewind_and_destroy_while_the_feeder_is_running(hostapi, oracle, tmp_pat
     p.close()                                         # destroyed mid-pass
     for _ in range(3):                                # created and dropped without a single Next()
         hostapi.CppParser(str(f), 0, 1, "libsvm", 4).close()
+
+
+def test_row_block_iter_drops_uri_arguments_like_the_reference(hostapi, oracle, tmp_path):
+    """Reference quirk kept on purpose: CreateIter_ hands CreateParser_ the URI *without* its
+    "?key=value" part (src/data.cc:95-97), so through RowBlockIter::Create a CSV file never has a
+    label column and type "auto" never sees format=.  Parser::Create keeps the arguments."""
+    f = tmp_path / "t.csv"
+    rnd = random.Random(5)
+    f.write_text("".join(",".join("%.3f" % rnd.uniform(-5, 5) for _ in range(20)) + "\n" for _ in range(300)))
+    uri = str(f) + "?format=csv&label_column=0"
+    got, ncol, _ = hostapi.row_iter(uri, 0, 1, "csv", 4)
+    exp = oracle.parse_buffer("csv", f.read_bytes(), 4, -1)          # no label column
+    assert same_rowblocks(got, exp) is None and ncol == 20
+    assert not got["label"].any()
+    with_args, _ = hostapi.CppParser(uri, 0, 1, "csv", 4).drain()    # Parser::Create honours them
+    assert same_rowblocks(with_args, oracle.parse_buffer("csv", f.read_bytes(), 4, 0)) is None
+    g = tmp_path / "positive.csv"     # read as LibSVM a '-' would be a negative index: keep it parseable
+    g.write_text("".join(",".join("%.3f" % rnd.uniform(0.5, 5) for _ in range(20)) + "\n" for _ in range(300)))
+    uri_g = str(g) + "?format=csv&label_column=0"
+    as_svm, _, _ = hostapi.row_iter(uri_g, 0, 1, "auto", 4)          # "auto" -> libsvm, format= lost
+    assert same_rowblocks(as_svm, oracle.parse_buffer("libsvm", g.read_bytes(), 4)) is None
+    from oracle.pyoracle import Reference
+    reference = Reference.load()       # present on the GPU box when oracle/_ref travelled along
+    if reference is not None:
+        theirs, their_ncol = reference.iter_uri(uri, 0, 1, "csv", 4)
+        assert same_rowblocks(got, theirs) is None and their_ncol == ncol
+        theirs, _ = reference.iter_uri(uri_g, 0, 1, "auto", 4)
+        assert same_rowblocks(as_svm, theirs) is None
