@@ -242,9 +242,11 @@ def main():
         raise SystemExit("bench.py needs a GPU (there is no CPU path)")
     torch.cuda.set_device(local)
     if world > 1:
-        # NCCL_DEBUG=VERSION (set on some boxes) makes NCCL print a banner on stdout, which must
-        # carry exactly one JSON line
-        os.environ["NCCL_DEBUG"] = "WARN"
+        # stdout must carry exactly one JSON line: NCCL prints its version banner there at any
+        # debug level from VERSION up (WARN included), so switch its logging off and point
+        # whatever is left at stderr
+        os.environ.pop("NCCL_DEBUG", None)
+        os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():

@@ -537,9 +537,12 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->pool = NULL;
   h->copied_h2d = h->copied_d2h = 0;
   {
-    /* default: a quarter of the host's cores, at most four (B200P_HOST_THREADS overrides) */
+    /* default: a quarter of the host's cores, at most four, shared fairly between the ranks of
+       one host when a launcher says how many there are (B200P_HOST_THREADS overrides) */
     const unsigned hw = std::thread::hardware_concurrency();
-    int n = static_cast<int>(std::min(4u, std::max(1u, hw / 4u)));
+    const char *local = std::getenv("LOCAL_WORLD_SIZE");
+    const unsigned ranks = (local != NULL && std::atoi(local) > 0) ? static_cast<unsigned>(std::atoi(local)) : 1u;
+    int n = static_cast<int>(std::min(4u, std::max(1u, hw / 4u / ranks)));
     const char *env = std::getenv("B200P_HOST_THREADS");
     if (env != NULL && env[0] != '\0') n = std::atoi(env);
     h->host_threads = std::max(0, std::min(n, 64));

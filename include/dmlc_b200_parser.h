@@ -140,7 +140,8 @@ int b200p_pending(b200p_handle h);
  * non-label field of a row has column id j, src/data/csv_parser.h:84-88) -- but written into the
  * pinned result by these threads while value[] is still on the link; that halves the
  * device-to-host bytes of the path. 0 = always copy index[] from the GPU. Default: a quarter of
- * the host's cores, at most 4; the environment variable B200P_HOST_THREADS overrides the default.
+ * the host's cores (divided by LOCAL_WORLD_SIZE when a launcher exports it), at most 4; the
+ * environment variable B200P_HOST_THREADS overrides the default.
  * The arrays returned are identical either way. No reference counterpart.
  */
 int b200p_set_host_threads(b200p_handle h, int threads);
