@@ -1,11 +1,13 @@
 #!/usr/bin/env python
-"""Device-resident throughput of the five BASELINE.json corpus shapes (one B200), per kernel.
+"""Throughput of the five BASELINE.json corpus shapes on one B200: device-resident per kernel, and
+end to end through b200p_submit / b200p_next (pinned host text in, pinned host CSR out).
 Not the contract bench (that is bench.py on configs[1]); this is the per-format evidence for
-profiles/.   python tools/bench_formats.py [--mb 512] [--range-bytes 0]"""
+profiles/.   python tools/bench_formats.py [--mb 512] [--range-bytes 0] [--no-e2e]"""
 import argparse
 import json
 import os
 import sys
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -22,12 +24,52 @@ SHAPES = [  # BASELINE config, generator kind, format, index bytes, label column
 ]
 
 
+def end_to_end(data, fmt, ib, lc, args):
+    """The same text from pinned host memory through b200p_submit / b200p_next, `passes` times."""
+    host = torch.from_numpy(data).pin_memory()
+    raw = host.numpy()
+    base = host.data_ptr()
+    step = args.chunk_mb << 20
+    cuts, pos = [0], 0
+    while pos < raw.size:
+        pos = min(raw.size, pos + step)
+        while pos < raw.size and raw[pos - 1] != 10:
+            pos -= 1
+        cuts.append(pos)
+    depth = 3
+    p = Parser(fmt, index_bytes=ib, label_column=lc, chunk_bytes=step, depth=depth)
+
+    def one_pass():
+        rows = 0
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            while p.pending() >= depth:
+                rows += p.next_raw().rows
+            p.submit_in_place(base + a, b - a)
+        while p.pending():
+            rows += p.next_raw().rows
+        return rows
+
+    one_pass()
+    up0, down0 = p.copied_bytes()
+    t0 = time.perf_counter()
+    passes = 4
+    for _ in range(passes):
+        one_pass()
+    dt = (time.perf_counter() - t0) / passes
+    up1, down1 = p.copied_bytes()
+    p.close()
+    return {"e2e_GBps": raw.size / dt / 1e9, "e2e_h2d_bytes": (up1 - up0) // passes,
+            "e2e_d2h_bytes": (down1 - down0) // passes}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mb", type=int, default=512)
     ap.add_argument("--range-bytes", type=int, default=0)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--only", default="", help="substring of the shape name to run")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--chunk-mb", type=int, default=64)
     args = ap.parse_args()
     peak = 6540.8
     try:
@@ -63,9 +105,11 @@ def main():
                     "input_GBps": dev.numel() / total / 1e6, "b_alg": int(b_alg),
                     "emit_frac_of_hbm_peak": b_alg / ms[2] / 1e6 / peak,
                     "all_kernels_frac_of_hbm_peak": b_alg / total / 1e6 / peak})
-        print(json.dumps(out[-1]))
         p.close()
         del dev
+        if not args.no_e2e:
+            out[-1].update(end_to_end(data, fmt, ib, lc, args))
+        print(json.dumps(out[-1]))
     return out
 
 
