@@ -85,7 +85,7 @@ class B200TextParser : public Parser<IndexType> {
         feeder_done_(false) {
     std::memset(&block_, 0, sizeof(block_));
 #if B200_HAVE_TEXT_SPLIT
-    text_ = dynamic_cast<TextSplit *>(source);
+    text_ = dynamic_cast<LineSource *>(source);   /* TextSplit or StdinSplit */
 #endif
     b200p_config cfg;
     std::memset(&cfg, 0, sizeof(cfg));
@@ -108,7 +108,8 @@ class B200TextParser : public Parser<IndexType> {
     if (text_ == NULL) source_->HintChunkSize(chunk_bytes_);
 #if B200_HAVE_TEXT_SPLIT
     if (text_ != NULL && EnvInt("DMLC_B200_READ_THREADS", 0) > 0) {
-      text_->SetReadThreads(EnvInt("DMLC_B200_READ_THREADS", 0));
+      TextSplit *files = dynamic_cast<TextSplit *>(source);
+      if (files != NULL) files->SetReadThreads(EnvInt("DMLC_B200_READ_THREADS", 0));
     }
 #endif
   }
@@ -173,17 +174,17 @@ class B200TextParser : public Parser<IndexType> {
     BlockMax(&mi, &mf);
     return mi;
   }
-  /* text bytes of this parser's partition when the source can tell (TextSplit), else 0 */
+  /* text bytes of this parser's partition when the source can tell (files), else 0 */
   size_t PartitionBytes() const {
 #if B200_HAVE_TEXT_SPLIT
-    if (text_ != NULL) return static_cast<size_t>(text_->PartitionEnd() - text_->PartitionBegin());
+    if (text_ != NULL) return static_cast<size_t>(text_->PassBytes());
 #endif
     return 0;
   }
 
  private:
   /*
-   * TextSplit sources.  The feeder thread loops { borrow the pinned staging buffer of a free
+   * Sources that can fill pinned memory themselves (TextSplit, StdinSplit).  The feeder thread loops { borrow the pinned staging buffer of a free
    * pipeline slot; fill it with the next whole lines of the partition (parallel pread);
    * b200p_submit } whenever fewer than `depth` chunks are in flight; the consumer thread only
    * calls b200p_next.  The C ABI allows exactly this pairing of threads on one handle.  An
@@ -210,7 +211,7 @@ class B200TextParser : public Parser<IndexType> {
         Check(rc);
         size_t n = text_->ReadLines(pinned, static_cast<size_t>(cap));
         const void *chunk = pinned;
-        if (n == TextSplit::kLineTooLong) {
+        if (n == LineSource::kLineTooLong) {
           /* a single line longer than the staging buffer: read it through a growing heap
              buffer; b200p_submit then enlarges the slot */
           size_t big = static_cast<size_t>(cap);
@@ -219,7 +220,7 @@ class B200TextParser : public Parser<IndexType> {
             CHECK(big <= B200P_MAX_CHUNK_BYTES) << "a single line exceeds " << B200P_MAX_CHUNK_BYTES << " bytes";
             spill_.resize(big);
             n = text_->ReadLines(spill_.data(), big);
-          } while (n == TextSplit::kLineTooLong);
+          } while (n == LineSource::kLineTooLong);
           chunk = spill_.data();
         }
         /* at the end of the partition an empty chunk hands the borrowed buffer back (it comes
@@ -312,7 +313,7 @@ class B200TextParser : public Parser<IndexType> {
 
   InputSplit *source_;
 #if B200_HAVE_TEXT_SPLIT
-  TextSplit *text_;
+  LineSource *text_;   /* the source again, when it can fill pinned memory itself */
 #else
   void *text_;
 #endif

@@ -265,24 +265,111 @@ bool TextSplit::NextChunk(Blob *out_chunk) {
   }
 }
 
+/* records are served out of chunks (reference LineSplitter::ExtractNextRecord,
+   src/io/line_split.cc:36-55): a record is the line plus the EOL run that follows it; the last
+   byte of that run (or the byte after the chunk) is overwritten by NUL.  `base` has one spare
+   byte behind `end`. */
+static void CutRecord(char *base, size_t *pos, size_t end, InputSplit::Blob *out_rec) {
+  size_t p = *pos;
+  while (p != end && !IsEol(base[p])) ++p;
+  while (p != end && IsEol(base[p])) ++p;
+  if (p == end) base[p] = '\0'; else base[p - 1] = '\0';
+  out_rec->dptr = base + *pos;
+  out_rec->size = p - *pos;
+  *pos = p;
+}
+
 bool TextSplit::NextRecord(Blob *out_rec) {
-  /* records are served out of chunks (reference LineSplitter::ExtractNextRecord,
-     src/io/line_split.cc:36-55): a record is the line plus the EOL run that follows it; the last
-     byte of that run (or the byte after the chunk) is overwritten by NUL */
   while (rec_pos_ == rec_end_) {
     Blob chunk;
     if (!NextChunk(&chunk)) return false;
     rec_pos_ = 0;
     rec_end_ = chunk.size;
   }
-  char *base = chunk_.data();
-  size_t p = rec_pos_;
-  while (p != rec_end_ && !IsEol(base[p])) ++p;
-  while (p != rec_end_ && IsEol(base[p])) ++p;
-  if (p == rec_end_) base[p] = '\0'; else base[p - 1] = '\0';
-  out_rec->dptr = base + rec_pos_;
-  out_rec->size = p - rec_pos_;
-  rec_pos_ = p;
+  CutRecord(chunk_.data(), &rec_pos_, rec_end_, out_rec);
+  return true;
+}
+
+/* ------------------------------------------------------------------------- stdin ---------- */
+StdinSplit::StdinSplit() : eof_(false), chunk_size_hint_(8u << 20), rec_pos_(0), rec_end_(0) {}
+
+void StdinSplit::HintChunkSize(size_t chunk_size) {
+  chunk_size_hint_ = std::max<size_t>(chunk_size, 1u << 18);
+}
+
+size_t StdinSplit::GetTotalSize(void) {
+  struct stat st;
+  return fstat(0, &st) == 0 ? static_cast<size_t>(st.st_size) : 0;
+}
+
+void StdinSplit::BeforeFirst(void) {
+  if (lseek(0, 0, SEEK_SET) == 0) {   /* a redirected file; a pipe cannot be replayed */
+    carry_.clear();
+    eof_ = false;
+  }
+  rec_pos_ = rec_end_ = 0;
+}
+
+void StdinSplit::ResetPartition(unsigned part_index, unsigned num_parts) {
+  CHECK(part_index == 0 && num_parts == 1) << "stdin cannot be partitioned";
+  BeforeFirst();
+}
+
+size_t StdinSplit::ReadLines(void *buf, size_t cap) {
+  char *dst = static_cast<char *>(buf);
+  if (carry_.size() >= cap && cap != 0) {
+    /* more is waiting than fits: serve whole lines out of the carry alone */
+    size_t cut = cap;
+    while (cut > 0 && !IsEol(carry_[cut - 1])) --cut;
+    if (cut == 0) return kLineTooLong;
+    std::memcpy(dst, carry_.data(), cut);
+    carry_.erase(carry_.begin(), carry_.begin() + cut);
+    return cut;
+  }
+  size_t have = carry_.size();
+  if (have != 0) std::memcpy(dst, carry_.data(), have);
+  carry_.clear();
+  while (!eof_ && have < cap) {
+    const ssize_t got = read(0, dst + have, cap - have);
+    if (got < 0 && errno == EINTR) continue;
+    CHECK(got >= 0) << "read from stdin failed: " << strerror(errno);
+    if (got == 0) eof_ = true;
+    have += static_cast<size_t>(got);
+  }
+  if (eof_) return have;            /* the rest of the stream, with or without a final EOL */
+  size_t cut = have;
+  while (cut > 0 && !IsEol(dst[cut - 1])) --cut;
+  carry_.assign(dst + cut, dst + have);   /* the unfinished line waits for the next call */
+  if (cut == 0) return kLineTooLong;
+  return cut;
+}
+
+bool StdinSplit::NextChunk(Blob *out_chunk) {
+  size_t cap = chunk_size_hint_;
+  for (;;) {
+    if (chunk_.size() < cap + 1) chunk_.resize(cap + 1);
+    const size_t n = ReadLines(chunk_.data(), cap);
+    if (n == kLineTooLong) {
+      cap *= 2;
+      continue;
+    }
+    if (n == 0) return false;
+    chunk_[n] = '\0';
+    out_chunk->dptr = chunk_.data();
+    out_chunk->size = n;
+    rec_pos_ = rec_end_ = 0;
+    return true;
+  }
+}
+
+bool StdinSplit::NextRecord(Blob *out_rec) {
+  while (rec_pos_ == rec_end_) {
+    Blob chunk;
+    if (!NextChunk(&chunk)) return false;
+    rec_pos_ = 0;
+    rec_end_ = chunk.size;
+  }
+  CutRecord(chunk_.data(), &rec_pos_, rec_end_, out_rec);
   return true;
 }
 
@@ -291,6 +378,7 @@ bool TextSplit::NextRecord(Blob *out_rec) {
 InputSplit *InputSplit::Create(const char *uri, unsigned part_index, unsigned num_parts,
                                const char *type) {
   b200::UriSpec spec(uri, part_index, num_parts);
+  if (spec.uri == "stdin") return new b200::StdinSplit();   /* before the part check, like io.cc:96-99 */
   CHECK(part_index < num_parts) << "invalid input parameter for InputSplit::Create";
   CHECK(!strcmp(type, "text")) << "unknown input split type " << type
                                << " (dmlc_core_b200 provides the \"text\" split only)";

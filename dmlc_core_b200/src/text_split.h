@@ -29,9 +29,26 @@ class HostPool;
 namespace dmlc {
 namespace b200 {
 
-class TextSplit : public InputSplit {
+/*
+ * What the GPU parser's feeder thread needs from a source: whole lines written straight into
+ * memory it names (the pinned staging buffer of a pipeline slot).
+ */
+class LineSource {
  public:
   static const size_t kLineTooLong = static_cast<size_t>(-1);
+  virtual ~LineSource() {}
+  /*
+   * Fill `buf` (capacity `cap`) with the next run of whole lines.  Returns the number of bytes
+   * (0 at the end) or kLineTooLong when not even one line fits in `cap` (retry with a larger
+   * buffer; nothing is lost).
+   */
+  virtual size_t ReadLines(void *buf, size_t cap) = 0;
+  /* bytes this source will deliver in one pass, 0 when it cannot know (a pipe) */
+  virtual uint64_t PassBytes() const = 0;
+};
+
+class TextSplit : public InputSplit, public LineSource {
+ public:
 
   TextSplit(const char *uri, unsigned part_index, unsigned num_parts);
   virtual ~TextSplit();
@@ -43,12 +60,8 @@ class TextSplit : public InputSplit {
   virtual bool NextChunk(Blob *out_chunk);
   virtual void ResetPartition(unsigned part_index, unsigned num_parts);
 
-  /*
-   * Fill `buf` (capacity `cap`) with the next run of whole lines of this partition.
-   * Returns the number of bytes (0 at the end of the partition) or kLineTooLong when not even
-   * one line fits in `cap` (nothing consumed; retry with a larger buffer).
-   */
-  size_t ReadLines(void *buf, size_t cap);
+  virtual size_t ReadLines(void *buf, size_t cap);
+  virtual uint64_t PassBytes() const { return end_ - begin_; }
 
   /* adjusted byte range of the partition within the logical stream */
   uint64_t PartitionBegin() const { return begin_; }
@@ -75,6 +88,32 @@ class TextSplit : public InputSplit {
   int read_threads_;
   b200p::HostPool *pool_;   /* readers of ReadRange, created on first use */
   /* NextChunk / NextRecord state */
+  std::vector<char> chunk_;
+  size_t chunk_size_hint_;
+  size_t rec_pos_, rec_end_;
+};
+
+/*
+ * "stdin": the lines arriving on file descriptor 0, as one unpartitioned stream (the job of the
+ * reference's SingleFileSplit, src/io/single_file_split.h:27-170, reached through
+ * InputSplit::Create("stdin", ...), src/io.cc:96-98).  BeforeFirst rewinds when stdin is a
+ * regular file and is a no-op on a pipe, where the reference's fseek fails just as silently.
+ */
+class StdinSplit : public InputSplit, public LineSource {
+ public:
+  StdinSplit();
+  virtual void HintChunkSize(size_t chunk_size);
+  virtual size_t GetTotalSize(void);
+  virtual void BeforeFirst(void);
+  virtual bool NextRecord(Blob *out_rec);
+  virtual bool NextChunk(Blob *out_chunk);
+  virtual void ResetPartition(unsigned part_index, unsigned num_parts);
+  virtual size_t ReadLines(void *buf, size_t cap);
+  virtual uint64_t PassBytes() const { return 0; }
+
+ private:
+  std::vector<char> carry_;   /* bytes read from the descriptor but not handed out yet */
+  bool eof_;
   std::vector<char> chunk_;
   size_t chunk_size_hint_;
   size_t rec_pos_, rec_end_;

@@ -267,3 +267,25 @@ def test_row_block_iter_drops_uri_arguments_like_the_reference(hostapi, oracle, 
         assert same_rowblocks(got, theirs) is None and their_ncol == ncol
         theirs, _ = reference.iter_uri(uri_g, 0, 1, "auto", 4)
         assert same_rowblocks(as_svm, theirs) is None
+
+
+def test_parser_on_stdin(hostapi, oracle, tmp_path):
+    """Parser::Create("stdin", 0, 1, type): the `cat file | program stdin` use of the reference
+    (SingleFileSplit behind InputSplit::Create, src/io.cc:96-98).  The feeder thread reads the
+    pipe straight into the pinned staging buffers; result equals the oracle on the same bytes."""
+    import subprocess
+    import sys
+    from dmlc_core_b200 import datagen
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    data, rows = datagen.generate("libsvm", 41, 9 << 20)
+    exp = oracle.parse_buffer("libsvm", data.tobytes(), 4)
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); from dmlc_core_b200 import hostapi; "
+            "got, n = hostapi.CppParser('stdin', 0, 1, 'libsvm', 4).drain(); "
+            "np.savez(sys.argv[1], nblocks=n, **{k: v for k, v in got.items() if hasattr(v, 'dtype')})" % root)
+    out = tmp_path / "got.npz"
+    env = dict(os.environ, DMLC_B200_CHUNK_MB="1")
+    subprocess.run([sys.executable, "-c", code, str(out)], input=data.tobytes(), check=True, env=env)
+    z = np.load(out)
+    got = {k: z[k] for k in ("offset", "label", "weight", "qid", "field", "index", "value")}
+    got["error"] = 0
+    assert same_rowblocks(got, exp) is None and int(z["nblocks"]) >= 6

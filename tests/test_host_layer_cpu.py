@@ -120,3 +120,35 @@ def test_cache_written_by_the_reference_loads_here(hostapi, reference, oracle, t
         exp = oracle.parse_buffer(fmt, data.tobytes(), ib)
         assert same_rowblocks(got, exp) is None
         assert ncol == int(exp["index"].max()) + 1
+
+
+def test_stdin_source(hostapi, tmp_path):
+    """InputSplit::Create("stdin", ...) (reference src/io.cc:96-98 -> SingleFileSplit): the lines
+    arriving on descriptor 0, through a pipe and from a redirected file, as chunks of whole lines
+    and as records; a line longer than the chunk hint grows the chunk."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    rnd = random.Random(9)
+    lines = [" ".join("%d:%d" % (rnd.randint(1, 99999), rnd.randint(0, 9)) for _ in range(rnd.randint(0, 40)))
+             for _ in range(20000)]
+    lines[700] = "7 " + "1:1 " * 200000            # ~800 KB line, longer than the 256 KiB minimum chunk
+    text = ("\n".join(lines) + "\n").encode()
+    code = ("import sys; sys.path.insert(0, %r); from dmlc_core_b200 import hostapi; "
+            "b, n = hostapi.split_bytes('stdin', 0, 1, mode=int(sys.argv[1]), chunk_hint=1 << 18); "
+            "sys.stdout.buffer.write(b); sys.stderr.write(str(n))" % root)
+    for mode in (0, 1):
+        piped = subprocess.run([sys.executable, "-c", code, str(mode)], input=text, capture_output=True, check=True)
+        pieces = int(piped.stderr.decode().strip().split()[-1])
+        if mode == 0:
+            assert piped.stdout == text and pieces > 3
+        else:
+            # a record keeps the EOL bytes the reference's ExtractNextRecord leaves in it (all but
+            # the last of its run, or all of them at the end of a chunk): compare line by line
+            kept = [x.encode() for x in lines if x]
+            assert [x for x in piped.stdout.split(b"\n") if x] == kept and pieces == len(kept)
+    f = tmp_path / "in.txt"
+    f.write_bytes(text[:-1])                         # last line without an EOL
+    with open(f, "rb") as fh:
+        redirected = subprocess.run([sys.executable, "-c", code, "0"], stdin=fh, capture_output=True, check=True)
+    assert redirected.stdout == text[:-1]
