@@ -1,6 +1,7 @@
 """GPU parity suite (-m gpu): the CUDA path, called through the C ABI, against the oracle
 (oracle/dmlc_oracle.c) and the committed golden RowBlocks of the unmodified reference.
 Bit-exact for every array; floats are compared as IEEE bit patterns (tolerance: 0 ulp)."""
+import os
 import random
 import time
 
@@ -66,11 +67,13 @@ def test_adversarial_fuzz(cuda_lib, oracle, fmt, ib):
     """Random separators / odd tokens / CRLF / qid / chains, small and multi-range inputs.
     The trailing-colon-at-end-of-line form is excluded: the reference reads past the line there
     (declared malformed); every other quirk must match, including which inputs throw."""
-    rnd = random.Random(1234 + ib + len(fmt))
+    # B200_FUZZ_SEED / B200_FUZZ_CASES widen the run (the round's long soak used 3 seeds x 10000)
+    rnd = random.Random(int(os.environ.get("B200_FUZZ_SEED", "1234")) + ib + len(fmt))
+    cases = int(os.environ.get("B200_FUZZ_CASES", "500"))
     lc = 1 if fmt == "csv" else -1
     parsers = [_parser(cuda_lib, fmt, ib, lc, range_bytes=rb) for rb in (512, 1024, 0)]
     done = 0
-    while done < 500:
+    while done < cases:
         text = _random_text(rnd, rnd.choice([1, 3, 10, 60, 300]))
         bad = False
         for line in text.replace(b"\r", b"\n").split(b"\n"):
