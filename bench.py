@@ -303,6 +303,7 @@ def main():
     for _ in range(args.steps):
         device_step()
     ev1.record(stream)
+    launches = p.launch_count() - launches0     # kernels enqueued inside the timed region
     barrier()
     # the timed region lasts tens of ms; keep the identical load running (untimed) until
     # nvidia-smi has delivered a few samples
@@ -313,7 +314,6 @@ def main():
     clocks = sampler.stop()
     clocks["window"] = "warm-up + timed steps + identical untimed steps until >= 4 samples"
     dev_ms = max_over_ranks(ev0.elapsed_time(ev1)) / args.steps
-    launches = p.launch_count() - launches0
     value = world * text_bytes / (dev_ms * 1e-3) / GB
 
     # ---------------- roofline of the dominant kernel (pass 2) ---------------------------------
@@ -427,6 +427,7 @@ def main():
         harr[:sample_bytes].tofile(path)
         nthread = os.cpu_count() or 1
         res = time_reference(path, nthread, args.cpu_seconds)
+        one = time_reference(path, 1, min(4.0, args.cpu_seconds)) if res is not None and nthread > 1 else None
         os.remove(path)
         if res is not None:
             cpu = {"value": res["bytes"] / res["per_pass"] / GB, "unit": "GB/s", "cores": nthread,
@@ -434,6 +435,8 @@ def main():
                    "sample": "first %d MB of the workload, %.1f s of passes, OMP threads=%d"
                              % (sample_bytes // 1000000, args.cpu_seconds, nthread),
                    "rows_per_s": res["rows"] / res["per_pass"]}
+            if one is not None:   # OMP_NUM_THREADS in {1, all cores}
+                cpu["single_thread_GBps"] = one["bytes"] / one["per_pass"] / GB
 
     if rank == 0:
         line = {

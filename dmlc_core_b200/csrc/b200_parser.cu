@@ -265,6 +265,14 @@ static void Provision(const b200p_handle h, uint64_t nbytes, uint64_t *rows, uin
 template <int FMT, typename IdxT>
 static void LaunchWalks(const WalkParams &p, cudaStream_t s, bool emit) {
   const unsigned grid = (p.num_ranges + kWarpsPerCta - 1) / kWarpsPerCta;
+#ifdef B200P_CARVEOUT   /* tuning experiments only: shared-memory share of the L1/shared array, percent */
+  static bool once = false;
+  if (!once) {
+    once = true;
+    cudaFuncSetAttribute(WalkText<FMT, IdxT, true>, cudaFuncAttributePreferredSharedMemoryCarveout, B200P_CARVEOUT);
+    cudaFuncSetAttribute(WalkText<FMT, IdxT, false>, cudaFuncAttributePreferredSharedMemoryCarveout, B200P_CARVEOUT);
+  }
+#endif
   if (emit) {
     WalkText<FMT, IdxT, true><<<grid, kCtaThreads, 0, s>>>(p);
   } else {
@@ -288,10 +296,11 @@ static void LaunchWalk(const b200p_handle h, const WalkParams &p, cudaStream_t s
 }
 
 /* Bytes of text one warp owns. Large ranges amortise the two partial steps at the ends of a range
-   (measured on the 1 GB CSV window: 8 KiB 1.24 ms, 16 KiB 1.18 ms, 32 KiB 1.17 ms per emit launch),
+   (measured on the 1 GB CSV window: 8 KiB 1.20 ms, 16 KiB 1.14 ms, 32 KiB 1.13 ms per emit launch),
    small chunks need small ranges to fill 148 SMs x ~48 resident warps. */
 static uint32_t RangeBytesFor(const b200p_handle h, uint64_t nbytes) {
   if (h->range_bytes != 0u) return h->range_bytes;
+  if (nbytes >= (512ull << 20)) return 32768u;
   if (nbytes >= (128ull << 20)) return 16384u;
   if (nbytes >= (32ull << 20)) return 8192u;
   return 4096u;

@@ -67,7 +67,10 @@ enum ErrorBits {
 #endif
 
 constexpr int kStepBytes = 512;        /* one warp step: 32 lanes x 16 B */
-constexpr int kWarpsPerCta = 8;
+#ifndef B200P_WARPS_PER_CTA   /* tuning experiments only */
+#define B200P_WARPS_PER_CTA 8
+#endif
+constexpr int kWarpsPerCta = B200P_WARPS_PER_CTA;
 constexpr int kCtaThreads = kWarpsPerCta * 32;
 constexpr int kTokenQueue = 320;       /* < 32 left over + <= 256 new digit runs per step */
 constexpr int kFieldQueue = 576;       /* CSV: < 32 left over + <= 512 field starts per step */
@@ -707,8 +710,7 @@ template <int FMT, typename IdxT, bool EMIT>
 __global__ void B200P_WALK_BOUNDS WalkText(const WalkParams prm) {
   __shared__ WarpScratch<FMT> scratch[kWarpsPerCta];
   __shared__ __align__(16) uint8_t lut[256];
-  static_assert(kCtaThreads == 256, "one thread fills one entry of the class table");
-  lut[threadIdx.x] = static_cast<uint8_t>(ClassEntry<FMT>(threadIdx.x));
+  for (int c = threadIdx.x; c < 256; c += kCtaThreads) lut[c] = static_cast<uint8_t>(ClassEntry<FMT>(c));
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
