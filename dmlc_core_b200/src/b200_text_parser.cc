@@ -106,12 +106,6 @@ class B200TextParser : public Parser<IndexType> {
       LOG(FATAL) << "dmlc_core_b200: cannot create the GPU parser: " << why;
     }
     if (text_ == NULL) source_->HintChunkSize(chunk_bytes_);
-#if B200_HAVE_TEXT_SPLIT
-    if (text_ != NULL && EnvInt("DMLC_B200_READ_THREADS", 0) > 0) {
-      TextSplit *files = dynamic_cast<TextSplit *>(source);
-      if (files != NULL) files->SetReadThreads(EnvInt("DMLC_B200_READ_THREADS", 0));
-    }
-#endif
   }
 
   virtual ~B200TextParser() {

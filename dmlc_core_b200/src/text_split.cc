@@ -43,6 +43,8 @@ TextSplit::TextSplit(const char *uri, unsigned part_index, unsigned num_parts)
   const char *local = std::getenv("LOCAL_WORLD_SIZE");
   const unsigned ranks = (local != NULL && std::atoi(local) > 0) ? static_cast<unsigned>(std::atoi(local)) : 1u;
   read_threads_ = static_cast<int>(std::max(1u, std::min(12u, hw * 3u / 4u / ranks)));
+  const char *forced = std::getenv("DMLC_B200_READ_THREADS");
+  if (forced != NULL && std::atoi(forced) > 0) read_threads_ = std::min(std::atoi(forced), 64);
   ExpandUri(uri);
   CHECK_NE(files_.size(), 0U) << "Cannot find any files that matches the URI pattern " << uri;
   start_.resize(files_.size() + 1);

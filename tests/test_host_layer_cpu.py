@@ -152,3 +152,21 @@ def test_stdin_source(hostapi, tmp_path):
     with open(f, "rb") as fh:
         redirected = subprocess.run([sys.executable, "-c", code, "0"], stdin=fh, capture_output=True, check=True)
     assert redirected.stdout == text[:-1]
+
+
+def test_large_chunks_go_through_the_reader_pool(hostapi, tmp_path, monkeypatch):
+    """Chunks of several MiB are read by the persistent reader pool (TextSplit::ReadRange fans a
+    chunk out in >= 2 MiB pieces): the bytes must come back complete and in order, for every
+    partition, also when the pool is rebuilt for another thread count."""
+    rnd = random.Random(77)
+    line = lambda: " ".join("%d:%.4f" % (rnd.randint(1, 10 ** 6), rnd.random()) for _ in range(rnd.randint(1, 30)))
+    text = ("\n".join(line() for _ in range(90000)) + "\n").encode()
+    assert len(text) > 18 << 20
+    f = tmp_path / "big.txt"
+    f.write_bytes(text)
+    for threads in ("3", "1", "7"):
+        monkeypatch.setenv("DMLC_B200_READ_THREADS", threads)
+        whole, pieces = hostapi.split_bytes(str(f), 0, 1, mode=0, chunk_hint=9 << 20, cap=len(text) + 64)
+        assert whole == text and 2 <= pieces <= 4
+    parts = [hostapi.split_bytes(str(f), k, 3, mode=0, chunk_hint=5 << 20, cap=len(text) + 64)[0] for k in range(3)]
+    assert b"".join(parts) == text and all(parts)
