@@ -37,7 +37,8 @@ class InputSplit {
   /* re-aim this split at another partition of the same files */
   virtual void ResetPartition(unsigned part_index, unsigned num_parts) = 0;
   /*
-   * uri: ';'-separated files and/or directories; type: "text".
+   * uri: ';'-separated files and/or directories, or "stdin"; "uri#cachefile" records the chunks of
+   * the first pass in cachefile and replays them afterwards; type: "text".
    * Part part_index of num_parts = bytes [ceil(T/n)*k, ceil(T/n)*(k+1)) of the concatenated
    * files, each end moved forward past the next end-of-line run unless it is a file start.
    */

@@ -375,6 +375,83 @@ bool StdinSplit::NextRecord(Blob *out_rec) {
   return true;
 }
 
+/* ------------------------------------------------------------------- "#cachefile" -------- */
+CachedSplit::CachedSplit(InputSplit *base, const std::string &cache_file)
+    : base_(base), cache_file_(cache_file), writer_(NULL), reader_(NULL), rec_pos_(0), rec_end_(0) {
+  if (!OpenForReplay()) {
+    writer_ = std::fopen(cache_file_.c_str(), "wb");
+    CHECK(writer_ != NULL) << "cannot create cache file " << cache_file_;
+  }
+}
+
+CachedSplit::~CachedSplit() {
+  if (writer_ != NULL) std::fclose(writer_);
+  if (reader_ != NULL) std::fclose(reader_);
+  delete base_;
+}
+
+bool CachedSplit::OpenForReplay() {
+  reader_ = std::fopen(cache_file_.c_str(), "rb");
+  return reader_ != NULL;
+}
+
+void CachedSplit::ResetPartition(unsigned, unsigned) {
+  LOG(FATAL) << "ResetPartition is not supported in CachedInputSplit";
+}
+
+void CachedSplit::BeforeFirst(void) {
+  if (writer_ != NULL) {
+    /* the recording pass must reach the end of the partition before the cache is complete */
+    Blob rest;
+    while (NextChunk(&rest)) {}
+    std::fclose(writer_);
+    writer_ = NULL;
+    CHECK(OpenForReplay()) << "Failed to initialize CachedIter";
+  } else {
+    std::rewind(reader_);
+  }
+  rec_pos_ = rec_end_ = 0;
+}
+
+bool CachedSplit::NextChunk(Blob *out_chunk) {
+  rec_pos_ = rec_end_ = 0;
+  if (writer_ != NULL) {
+    Blob blob;
+    if (!base_->NextChunk(&blob)) return false;
+    const size_t size = blob.size;
+    CHECK(std::fwrite(&size, sizeof(size), 1, writer_) == 1 &&
+          std::fwrite(blob.dptr, 1, size, writer_) == size) << "cannot write " << cache_file_;
+    /* own copy with a spare byte, so that records can be cut out of it */
+    chunk_.assign(static_cast<const char *>(blob.dptr), static_cast<const char *>(blob.dptr) + size);
+    chunk_.push_back('\0');
+    out_chunk->dptr = chunk_.data();
+    out_chunk->size = size;
+    return true;
+  }
+  size_t size = 0;
+  const size_t got = std::fread(&size, 1, sizeof(size), reader_);
+  if (got == 0) return false;
+  CHECK(got == sizeof(size)) << cache_file_ << " has invalid cache file format";
+  chunk_.resize(size + 1);
+  CHECK(std::fread(chunk_.data(), 1, size, reader_) == size)
+      << cache_file_ << " has invalid cache file format";
+  chunk_[size] = '\0';
+  out_chunk->dptr = chunk_.data();
+  out_chunk->size = size;
+  return true;
+}
+
+bool CachedSplit::NextRecord(Blob *out_rec) {
+  while (rec_pos_ == rec_end_) {
+    Blob chunk;
+    if (!NextChunk(&chunk)) return false;
+    rec_pos_ = 0;
+    rec_end_ = chunk.size;
+  }
+  CutRecord(chunk_.data(), &rec_pos_, rec_end_, out_rec);
+  return true;
+}
+
 }  // namespace b200
 
 InputSplit *InputSplit::Create(const char *uri, unsigned part_index, unsigned num_parts,
@@ -384,8 +461,9 @@ InputSplit *InputSplit::Create(const char *uri, unsigned part_index, unsigned nu
   CHECK(part_index < num_parts) << "invalid input parameter for InputSplit::Create";
   CHECK(!strcmp(type, "text")) << "unknown input split type " << type
                                << " (dmlc_core_b200 provides the \"text\" split only)";
-  CHECK(spec.cache_file.empty()) << "#cachefile splits are not provided by dmlc_core_b200";
-  return new b200::TextSplit(spec.uri.c_str(), part_index, num_parts);
+  InputSplit *files = new b200::TextSplit(spec.uri.c_str(), part_index, num_parts);
+  if (spec.cache_file.empty()) return files;
+  return new b200::CachedSplit(files, spec.cache_file);   /* io.cc:123-127 */
 }
 
 }  // namespace dmlc

@@ -19,6 +19,7 @@
 #include <dmlc/io.h>
 
 #include <cstdint>
+#include <cstdio>
 #include <string>
 #include <vector>
 
@@ -116,6 +117,35 @@ class StdinSplit : public InputSplit, public LineSource {
   bool eof_;
   std::vector<char> chunk_;
   size_t chunk_size_hint_;
+  size_t rec_pos_, rec_end_;
+};
+
+/*
+ * "uri#cachefile" for InputSplit::Create: the first pass over `base` also writes every chunk to
+ * the cache file; from the first BeforeFirst() on -- or from the start, when the file already
+ * exists -- chunks come from the cache and the original files are not touched again (the job of
+ * the reference's CachedInputSplit, src/io/cached_input_split.h:31-187).  The file is the
+ * reference's: per chunk a native size_t byte count, then the bytes (:157-160, :176-186), so
+ * caches can be swapped between the two implementations.
+ */
+class CachedSplit : public InputSplit {
+ public:
+  CachedSplit(InputSplit *base, const std::string &cache_file);
+  virtual ~CachedSplit();
+  virtual void HintChunkSize(size_t chunk_size) { base_->HintChunkSize(chunk_size); }
+  virtual size_t GetTotalSize(void) { return base_->GetTotalSize(); }
+  virtual void BeforeFirst(void);
+  virtual bool NextRecord(Blob *out_rec);
+  virtual bool NextChunk(Blob *out_chunk);
+  virtual void ResetPartition(unsigned part_index, unsigned num_parts);
+
+ private:
+  bool OpenForReplay();
+  InputSplit *base_;
+  std::string cache_file_;
+  std::FILE *writer_;   /* non-NULL while the first pass is being recorded */
+  std::FILE *reader_;   /* non-NULL once chunks come from the cache */
+  std::vector<char> chunk_;
   size_t rec_pos_, rec_end_;
 };
 

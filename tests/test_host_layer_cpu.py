@@ -170,3 +170,32 @@ def test_large_chunks_go_through_the_reader_pool(hostapi, tmp_path, monkeypatch)
         assert whole == text and 2 <= pieces <= 4
     parts = [hostapi.split_bytes(str(f), k, 3, mode=0, chunk_hint=5 << 20, cap=len(text) + 64)[0] for k in range(3)]
     assert b"".join(parts) == text and all(parts)
+
+
+def test_input_split_cache_file_is_interchangeable_with_the_reference(hostapi, reference, tmp_path):
+    """InputSplit::Create("uri#cachefile", ...) (reference CachedInputSplit,
+    src/io/cached_input_split.h): the first pass records the chunks, later passes and later
+    processes replay them without the original files; caches written by either implementation
+    are read by the other."""
+    rnd = random.Random(21)
+    paths = _files(tmp_path, rnd, 3, ["\n", "\r\n", "\n"])
+    uri = ";".join(paths)
+    total = sum(os.path.getsize(p) for p in paths)
+    for nparts in (1, 2):
+        for part in range(nparts):
+            want, _, _ = reference.split_bytes(uri, part, nparts, total + 64)
+            mine = tmp_path / ("mine%d" % nparts)
+            theirs = tmp_path / ("theirs%d" % nparts)
+            got, _ = hostapi.split_bytes("%s#%s" % (uri, mine), part, nparts, cap=total + 64)     # records
+            assert got == want
+            again, _ = hostapi.split_bytes("%s#%s" % (uri, mine), part, nparts, cap=total + 64)   # replays
+            assert again == want
+            ref_reads_mine, _, _ = reference.split_bytes("%s#%s" % (uri, mine), part, nparts, total + 64)
+            assert ref_reads_mine == want
+            ref_first, _, _ = reference.split_bytes("%s#%s" % (uri, theirs), part, nparts, total + 64)  # records
+            assert ref_first == want
+            i_read_theirs, _ = hostapi.split_bytes("%s#%s" % (uri, theirs), part, nparts, mode=1, cap=total + 64)
+            lines = lambda b: [x for x in b.replace(b"\r", b"\n").split(b"\n") if x]
+            assert lines(i_read_theirs) == lines(want)
+    decorated = sorted(p.name for p in tmp_path.iterdir() if p.name.startswith("mine2"))
+    assert decorated == ["mine2.split2.part0", "mine2.split2.part1"]      # URISpec's suffix, uri_spec.h:59-66
