@@ -71,7 +71,8 @@ static int DeviceFor(unsigned part_index) {
  * Environment knobs (GPU-side settings cannot ride in the URI: CSVParserParam::Init rejects
  * unknown keys, reference csv_parser.h:50 + parameter.h:405-418):
  *   DMLC_B200_DEVICE    CUDA device ordinal (default 0), or "auto" = part_index % DMLC_B200_NUM_DEVICES
- *   DMLC_B200_CHUNK_MB  chunk size in MiB (default 64; the reference uses 8, input_split_base.h:40)
+ *   DMLC_B200_CHUNK_MB  chunk size in MiB (default 64, less for partitions under 384 MiB; the
+ *                       reference uses 8, input_split_base.h:40)
  *   DMLC_B200_DEPTH     chunks in flight (default 3)
  *   DMLC_B200_READ_THREADS  threads of one parallel pread (default: 3/4 of the cores, at most 12,
  *                           divided by LOCAL_WORLD_SIZE)
@@ -95,6 +96,13 @@ class B200TextParser : public Parser<IndexType> {
     cfg.device = DeviceFor(part_index);
     chunk_bytes_ = static_cast<size_t>(std::max(1, EnvInt("DMLC_B200_CHUNK_MB", 64))) << 20;
     chunk_bytes_ = std::min<size_t>(chunk_bytes_, B200P_MAX_CHUNK_BYTES);
+    if (EnvInt("DMLC_B200_CHUNK_MB", 0) <= 0 && PartitionBytes() != 0) {
+      /* a small partition gets small chunks: the pinned staging and result buffers of the
+         pipeline slots are the start-up cost, and six chunks are enough to overlap read, copy
+         and parse (100 MB of LibSVM: first pass 150 ms with 64 MiB chunks, 3x less this way) */
+      const size_t sixth = (PartitionBytes() / 6 + (1u << 20)) >> 20 << 20;
+      chunk_bytes_ = std::min(chunk_bytes_, std::max<size_t>(sixth, 4u << 20));
+    }
     cfg.chunk_bytes = chunk_bytes_;
     depth_ = std::max(1, std::min(8, EnvInt("DMLC_B200_DEPTH", 3)));
     cfg.depth = depth_;
