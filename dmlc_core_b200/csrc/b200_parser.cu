@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -224,7 +225,28 @@ bool HugePagesOnOffer() {
 }
 }  // namespace
 
+/* B200P_TRACE=1: where the set-up time of a handle went, printed by b200p_destroy */
+static std::atomic<uint64_t> g_pinned_ns(0), g_pinned_bytes(0), g_device_ns(0), g_device_calls(0);
+static uint64_t NowNs() {
+  return static_cast<uint64_t>(std::chrono::duration_cast<std::chrono::nanoseconds>(
+      std::chrono::steady_clock::now().time_since_epoch()).count());
+}
+struct AllocTimer {
+  std::atomic<uint64_t> *into;
+  uint64_t t0;
+  explicit AllocTimer(std::atomic<uint64_t> *where) : into(where), t0(NowNs()) {}
+  ~AllocTimer() { *into += NowNs() - t0; }
+};
+
+static cudaError_t DeviceAlloc(void **out, uint64_t bytes) {
+  AllocTimer t(&g_device_ns);
+  ++g_device_calls;
+  return cudaMalloc(out, bytes);
+}
+
 static cudaError_t PinnedAlloc(void **out, uint64_t bytes) {
+  AllocTimer t(&g_pinned_ns);
+  g_pinned_bytes += bytes;
   const uint64_t kHuge = 2ull << 20;
   *out = NULL;
   if (bytes >= kHuge && HugePagesOnOffer()) {
@@ -234,6 +256,21 @@ static cudaError_t PinnedAlloc(void **out, uint64_t bytes) {
 #ifdef MADV_HUGEPAGE
       madvise(p, rounded, MADV_HUGEPAGE);
 #endif
+      /* first touch is where the kernel zero-fills the pages (7 of the 9 ms per 64 MiB): spread
+         it over a few threads before the pages are pinned */
+      const unsigned hw = std::thread::hardware_concurrency();
+      const uint64_t touchers = std::min<uint64_t>(std::min<uint64_t>(8, std::max(1u, hw / 2)), rounded / kHuge);
+      if (touchers > 1) {
+        std::vector<std::thread> crew;
+        const uint64_t per = (rounded / touchers + kHuge - 1) / kHuge * kHuge;
+        for (uint64_t i = 0; i < touchers; ++i) {
+          crew.emplace_back([=] {
+            volatile char *base = static_cast<volatile char *>(p);
+            for (uint64_t at = per * i; at < std::min(rounded, per * (i + 1)); at += 4096) base[at] = 0;
+          });
+        }
+        for (std::thread &th : crew) th.join();
+      }
       if (cudaHostRegister(p, rounded, cudaHostRegisterPortable) == cudaSuccess) {
         std::lock_guard<std::mutex> g(g_registered_mu);
         g_registered.push_back(p);
@@ -277,7 +314,7 @@ template <typename T>
 static cudaError_t AllocOne(T **p, uint64_t count, size_t elt, bool pinned) {
   void *v = NULL;
   cudaError_t e = pinned ? PinnedAlloc(&v, std::max<uint64_t>(count, 1) * elt)
-                         : cudaMalloc(&v, std::max<uint64_t>(count, 1) * elt);
+                         : DeviceAlloc(&v, std::max<uint64_t>(count, 1) * elt);
   *p = static_cast<T *>(v);
   return e;
 }
@@ -430,7 +467,7 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
     s->counts_cap = 0;
     const uint64_t cap = ranges + ranges / 4 + 64;
     /* per-range counters followed by the per-tile bases of the scan */
-    CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&s->d_counts),
+    CUDA_TRY(h, DeviceAlloc(reinterpret_cast<void **>(&s->d_counts),
                            (cap + cap / kScanTile + 2) * kNumCounters * sizeof(uint32_t)));
     s->counts_cap = cap;
   }
@@ -664,6 +701,11 @@ void b200p_destroy(b200p_handle h) {
   cudaFree(h->d_max);
   delete h->pool;
   delete h;
+  if (std::getenv("B200P_TRACE") != NULL) {
+    std::fprintf(stderr, "b200p trace: pinned allocations %.1f ms for %.0f MB, device allocations %.1f ms in %llu calls (process totals)\n",
+                 g_pinned_ns.load() * 1e-6, g_pinned_bytes.load() * 1e-6, g_device_ns.load() * 1e-6,
+                 static_cast<unsigned long long>(g_device_calls.load()));
+  }
 }
 
 uint64_t b200p_launch_count(b200p_handle h) { return h != NULL ? h->launches.load() : 0; }
@@ -813,7 +855,7 @@ static int PrepareSlot(b200p_handle h, int id, uint64_t nbytes) {
     s->text_cap = 0;
     const uint64_t cap = (want + 4095) / 4096 * 4096;
     CUDA_TRY(h, PinnedAlloc(reinterpret_cast<void **>(&s->h_text), cap));
-    CUDA_TRY(h, cudaMalloc(reinterpret_cast<void **>(&s->d_text), cap));
+    CUDA_TRY(h, DeviceAlloc(reinterpret_cast<void **>(&s->d_text), cap));
     s->text_cap = cap;
   }
   return B200P_OK;
