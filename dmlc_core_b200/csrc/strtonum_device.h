@@ -19,6 +19,8 @@
 
 #include <stdint.h>
 
+#include <type_traits>
+
 #if defined(__CUDACC__)
 #define B200P_HD __host__ __device__ __forceinline__
 #define B200P_D __device__ __forceinline__
@@ -404,53 +406,73 @@ B200P_HD float ToFloatFast(const Text &t, uint32_t p) {
   return ToFloat(t, p, 0);
 }
 
-/* unsigned token at p: 1..15 digits followed by a non-digit inside the window */
+/* 10^m for m = 0..3, out of one 64-bit constant */
+B200P_HD uint32_t TenTo(uint32_t m) {
+  return static_cast<uint32_t>(0x03e80064000a0001ull >> (16u * m)) & 0xffffu;
+}
+
+/* the first m (0..3) digit bytes of x as a number */
+B200P_HD uint32_t PackLeading(uint32_t x, uint32_t m) {
+  return Pack4(ShlClamp(x & 0x0f0f0f0fu, 32u - 8u * m), 0u);
+}
+
+/*
+ * Unsigned token at p: 1..23 digits followed by a non-digit, four digits per step (Pack4) and
+ * one multiplication per word instead of one per digit.  All arithmetic is in the ring the
+ * reference accumulates in (mod 2^32 through Str2T<uint32_t>, mod 2^64 for uint64_t,
+ * strtonum.h:103-190), so overlong numbers wrap to the same value.  Tokens of 16 digits and more
+ * (64-bit hashes) read two more words; 24 and more, a sign or a blank in front go to ToUint.
+ */
 template <bool WIDE>
 B200P_HD bool ToUintWindow(const Text &t, uint32_t p, uint64_t *out) {
   Window w;
   if (!LoadWindow(t, p, &w)) return false;
-  const uint32_t nd0 = NonDigitFlags(w.x0);
-  uint32_t n;
-  if (nd0 != 0u) {
-    n = static_cast<uint32_t>(FirstSet(nd0)) >> 3;
-    if (n == 0u) return false;              /* sign, whitespace, empty: general code */
-  } else {
-    const uint32_t nd1 = NonDigitFlags(w.x1);
-    if (nd1 != 0u) {
-      n = 4u + (static_cast<uint32_t>(FirstSet(nd1)) >> 3);
-    } else {
-      const uint32_t nd2 = NonDigitFlags(w.x2);
-      if (nd2 != 0u) {
-        n = 8u + (static_cast<uint32_t>(FirstSet(nd2)) >> 3);
-      } else {
-        const uint32_t nd3 = NonDigitFlags(w.x3);
-        if (nd3 == 0u) return false;        /* >= 16 digits */
-        n = 12u + (static_cast<uint32_t>(FirstSet(nd3)) >> 3);
-      }
-    }
+  typedef typename std::conditional<WIDE, uint64_t, uint32_t>::type Acc;
+  uint32_t flags = NonDigitFlags(w.x0);
+  if (flags != 0u) {
+    const uint32_t m = static_cast<uint32_t>(FirstSet(flags)) >> 3;
+    if (m == 0u) return false;              /* sign, whitespace, empty: general code */
+    *out = PackLeading(w.x0, m);
+    return true;
   }
-  const uint32_t y[4] = {w.x0 & 0x0f0f0f0fu, w.x1 & 0x0f0f0f0fu, w.x2 & 0x0f0f0f0fu,
-                         w.x3 & 0x0f0f0f0fu};
-  /* digits wrap modulo 2^32 / 2^64 exactly like the sequential accumulation */
-  if (WIDE) {
-    uint64_t v = 0;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (uint32_t i = 0; i < 15u; ++i) {
-      if (i < n) v = v * 10ull + ((y[i >> 2] >> ((i & 3u) * 8u)) & 0xffu);
-    }
-    *out = v;
-  } else {
-    uint32_t v = 0;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (uint32_t i = 0; i < 15u; ++i) {
-      if (i < n) v = v * 10u + ((y[i >> 2] >> ((i & 3u) * 8u)) & 0xffu);
-    }
-    *out = v;
+  uint32_t low = Pack4(w.x0 & 0x0f0f0f0fu, 0u);                  /* digits 0..3 */
+  flags = NonDigitFlags(w.x1);
+  if (flags != 0u) {
+    const uint32_t m = static_cast<uint32_t>(FirstSet(flags)) >> 3;
+    *out = low * TenTo(m) + PackLeading(w.x1, m);                 /* < 10^7 */
+    return true;
   }
+  low = low * 10000u + Pack4(w.x1 & 0x0f0f0f0fu, 0u);             /* digits 0..7, < 10^8 */
+  flags = NonDigitFlags(w.x2);
+  if (flags != 0u) {
+    const uint32_t m = static_cast<uint32_t>(FirstSet(flags)) >> 3;
+    *out = static_cast<Acc>(static_cast<Acc>(low) * TenTo(m) + PackLeading(w.x2, m));
+    return true;
+  }
+  Acc v = static_cast<Acc>(static_cast<Acc>(low) * 10000u + Pack4(w.x2 & 0x0f0f0f0fu, 0u));   /* 12 digits */
+  flags = NonDigitFlags(w.x3);
+  if (flags != 0u) {
+    const uint32_t m = static_cast<uint32_t>(FirstSet(flags)) >> 3;
+    *out = static_cast<Acc>(v * TenTo(m) + PackLeading(w.x3, m));
+    return true;
+  }
+  /* 16 digits and more: bytes 16..23 of the token */
+  const uint32_t a = p & ~3u, k = p & 3u;
+  if (a + 28u > t.size) return false;
+  const uint32_t w4 = Load4(t.data + a + 16), w5 = Load4(t.data + a + 20), w6 = Load4(t.data + a + 24);
+  const uint32_t x4 = BytesFrom(w4, w5, k), x5 = BytesFrom(w5, w6, k);
+  v = static_cast<Acc>(v * 10000u + Pack4(w.x3 & 0x0f0f0f0fu, 0u));                            /* 16 digits */
+  flags = NonDigitFlags(x4);
+  if (flags != 0u) {
+    const uint32_t m = static_cast<uint32_t>(FirstSet(flags)) >> 3;
+    *out = static_cast<Acc>(v * TenTo(m) + PackLeading(x4, m));
+    return true;
+  }
+  v = static_cast<Acc>(v * 10000u + Pack4(x4 & 0x0f0f0f0fu, 0u));                              /* 20 digits */
+  flags = NonDigitFlags(x5);
+  if (flags == 0u) return false;            /* 24 digits and more */
+  const uint32_t m = static_cast<uint32_t>(FirstSet(flags)) >> 3;
+  *out = static_cast<Acc>(v * TenTo(m) + PackLeading(x5, m));
   return true;
 }
 

@@ -89,7 +89,7 @@ def test_window_fast_paths_match_oracle(emul, oracle):
     assert fast_typ >= 4950, fast_typ
     n_u = 0
     for _ in range(60000):
-        tok = "".join(rnd.choice("0123456789") for _ in range(rnd.randint(0, 21)))
+        tok = "".join(rnd.choice("0123456789") for _ in range(rnd.randint(0, 27)))
         if rnd.random() < 0.1:
             tok = rnd.choice(["+", "-", " ", "."]) + tok
         lead = " " * rnd.randint(0, 9)
