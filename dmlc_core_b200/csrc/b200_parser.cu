@@ -50,6 +50,7 @@ struct Arrays {
   float *value;
   uint64_t cap_rows;  /* rows the row-sized arrays can hold (offset holds cap_rows + 1) */
   uint64_t cap_nnz;
+  void *block;        /* the one allocation all seven arrays are carved from */
   Arrays() { std::memset(this, 0, sizeof(*this)); }
 };
 
@@ -300,56 +301,54 @@ static void PinnedFree(void *p) {
 }
 
 static void FreeDeviceArrays(Arrays *a) {
-  cudaFree(a->offset); cudaFree(a->label); cudaFree(a->weight); cudaFree(a->qid);
-  cudaFree(a->field); cudaFree(a->index); cudaFree(a->value);
+  cudaFree(a->block);
   *a = Arrays();
 }
 static void FreeHostArrays(Arrays *a) {
-  PinnedFree(a->offset); PinnedFree(a->label); PinnedFree(a->weight); PinnedFree(a->qid);
-  PinnedFree(a->field); PinnedFree(a->index); PinnedFree(a->value);
+  PinnedFree(a->block);
   *a = Arrays();
 }
 
-template <typename T>
-static cudaError_t AllocOne(T **p, uint64_t count, size_t elt, bool pinned) {
-  void *v = NULL;
-  cudaError_t e = pinned ? PinnedAlloc(&v, std::max<uint64_t>(count, 1) * elt)
-                         : DeviceAlloc(&v, std::max<uint64_t>(count, 1) * elt);
-  *p = static_cast<T *>(v);
-  return e;
-}
-
-/* (Re)allocate so that `rows` rows and `nnz` entries fit. Caller has synchronised the stream. */
+/*
+ * (Re)allocate so that `rows` rows and `nnz` entries fit; contents are not kept.  The seven
+ * arrays of a set share one allocation (each starts on a 256-byte boundary): allocations are the
+ * start-up cost of a handle, pinned ones by the byte and device ones by the call.  Caller has
+ * synchronised the stream.
+ */
 static int EnsureArrays(b200p_handle h, Arrays *a, uint64_t rows, uint64_t nnz, bool pinned) {
+  if (a->block != NULL && rows <= a->cap_rows && nnz <= a->cap_nnz) return B200P_OK;
   const int fmt = h->cfg.format;
-  const size_t iw = h->cfg.index_bytes;
-  if (rows > a->cap_rows || a->offset == NULL) {
-    const uint64_t cap = rows + rows / 4 + 1024;
-    if (pinned) {
-      PinnedFree(a->offset); PinnedFree(a->label); PinnedFree(a->weight); PinnedFree(a->qid);
-    } else {
-      cudaFree(a->offset); cudaFree(a->label); cudaFree(a->weight); cudaFree(a->qid);
-    }
-    a->offset = NULL; a->label = NULL; a->weight = NULL; a->qid = NULL; a->cap_rows = 0;
-    CUDA_TRY(h, AllocOne(&a->offset, cap + 1, 8, pinned));
-    CUDA_TRY(h, AllocOne(&a->label, cap, 4, pinned));
-    if (fmt != B200P_FORMAT_CSV) CUDA_TRY(h, AllocOne(&a->weight, cap, 4, pinned));
-    if (fmt == B200P_FORMAT_LIBSVM) CUDA_TRY(h, AllocOne(&a->qid, cap, 8, pinned));
-    a->cap_rows = cap;
+  const uint64_t iw = h->cfg.index_bytes;
+  const uint64_t cap_rows = rows > a->cap_rows || a->block == NULL ? rows + rows / 4 + 1024 : a->cap_rows;
+  const uint64_t cap_nnz = nnz > a->cap_nnz || a->block == NULL ? nnz + nnz / 4 + 1024 : a->cap_nnz;
+  const bool has_weight = fmt != B200P_FORMAT_CSV, has_qid = fmt == B200P_FORMAT_LIBSVM;
+  const bool has_field = fmt == B200P_FORMAT_LIBFM;
+  const auto pad = [](uint64_t bytes) { return (bytes + 255) / 256 * 256; };
+  const uint64_t sizes[7] = {pad((cap_rows + 1) * 8), pad(cap_rows * 4), has_weight ? pad(cap_rows * 4) : 0,
+                             has_qid ? pad(cap_rows * 8) : 0, has_field ? pad(cap_nnz * iw) : 0,
+                             pad(cap_nnz * iw), pad(cap_nnz * 4)};
+  uint64_t total = 0;
+  for (int i = 0; i < 7; ++i) total += sizes[i];
+  if (pinned) PinnedFree(a->block); else cudaFree(a->block);
+  *a = Arrays();
+  void *block = NULL;
+  CUDA_TRY(h, pinned ? PinnedAlloc(&block, total) : DeviceAlloc(&block, total));
+  char *at = static_cast<char *>(block);
+  void *parts[7];
+  for (int i = 0; i < 7; ++i) {
+    parts[i] = sizes[i] != 0 ? at : NULL;
+    at += sizes[i];
   }
-  if (nnz > a->cap_nnz || a->index == NULL) {
-    const uint64_t cap = nnz + nnz / 4 + 1024;
-    if (pinned) {
-      PinnedFree(a->field); PinnedFree(a->index); PinnedFree(a->value);
-    } else {
-      cudaFree(a->field); cudaFree(a->index); cudaFree(a->value);
-    }
-    a->field = NULL; a->index = NULL; a->value = NULL; a->cap_nnz = 0;
-    if (fmt == B200P_FORMAT_LIBFM) CUDA_TRY(h, AllocOne(reinterpret_cast<char **>(&a->field), cap, iw, pinned));
-    CUDA_TRY(h, AllocOne(reinterpret_cast<char **>(&a->index), cap, iw, pinned));
-    CUDA_TRY(h, AllocOne(&a->value, cap, 4, pinned));
-    a->cap_nnz = cap;
-  }
+  a->block = block;
+  a->offset = static_cast<unsigned long long *>(parts[0]);
+  a->label = static_cast<float *>(parts[1]);
+  a->weight = static_cast<float *>(parts[2]);
+  a->qid = static_cast<unsigned long long *>(parts[3]);
+  a->field = parts[4];
+  a->index = parts[5];
+  a->value = static_cast<float *>(parts[6]);
+  a->cap_rows = cap_rows;
+  a->cap_nnz = cap_nnz;
   return B200P_OK;
 }
 
