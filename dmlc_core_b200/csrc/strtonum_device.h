@@ -385,11 +385,21 @@ B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
     } else {
       const uint32_t r1 = BytesFrom(b, c, f0 & 3u);
       const uint32_t ndr1 = NonDigitFlags(r1);
-      if (ndr1 == 0u) return false;          /* >= 8 fraction digits */
-      const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr1)) & ~7u;
-      n2 = 4u + (bit >> 3);
-      term = (r1 >> bit) & 0xffu;
-      f8 = Pack4(r1 & 0x0f0f0f0fu & ((1u << bit) - 1u), Pack4(r0 & 0x0f0f0f0fu, 0u) * 10000u);
+      const uint32_t high = Pack4(r0 & 0x0f0f0f0fu, 0u) * 10000u;
+      if (ndr1 != 0u) {
+        const uint32_t bit = static_cast<uint32_t>(FirstSet(ndr1)) & ~7u;
+        n2 = 4u + (bit >> 3);
+        term = (r1 >> bit) & 0xffu;
+        f8 = Pack4(r1 & 0x0f0f0f0fu & ((1u << bit) - 1u), high);
+      } else {
+        /* exactly eight digits ("%.6g" of 0.00123456): the terminator is the next byte, which is
+           byte (f0 & 3) of the third word (the f0 + n2 test below rejects the case where that
+           word lies outside the window) */
+        n2 = 8u;
+        term = (c >> (8u * (f0 & 3u))) & 0xffu;
+        if (term - '0' < 10u) return false;    /* nine fraction digits and more */
+        f8 = Pack4(r1 & 0x0f0f0f0fu, high);
+      }
     }
     if (f0 + n2 > 15u) return false;         /* the terminator must be a real byte of the window */
     v = AddRn(v, Fraction8(f8));

@@ -56,7 +56,13 @@ def test_window_fast_paths_match_oracle(emul, oracle):
     fast_f = fast_u = total = 0
     toks = ["-7.60915", "0.137604", "7", "-", "+", ".", "-.5", "5.", "1234567.1234567", "12345678.5",
             "0.12345678", "16777217", "1e5", "2.5e-3", "9999999.9999999", "-0", "007.500", " 5", "\t1",
-            "0.0000001", "1.", "+1.5", "--5", "1.2.3", "0.", "-1234567.1234567", "+1234567.1234567"]
+            "0.0000001", "1.", "+1.5", "--5", "1.2.3", "0.", "-1234567.1234567", "+1234567.1234567",
+            # exactly eight fraction digits (what %.6g prints for 0.00123456), nine, and long forms
+            "0.00123456", "-0.00123456", "+0.00999999", "12.12345678", "123456.12345678",
+            "1234567.12345678", "0.123456789", "0.99999999", "0.999999999", "9.00000001", ".12345678"]
+    for _ in range(4000):
+        toks.append("%s%d.%s" % (rnd.choice(["", "-", "+"]), rnd.randint(0, 10 ** rnd.randint(0, 7)),
+                                 "".join(rnd.choice("0123456789") for _ in range(rnd.choice([7, 8, 8, 8, 9])))))
     for _ in range(60000):
         k = rnd.random()
         if k < 0.4:
