@@ -264,6 +264,9 @@ B200P_D float U32ToFloat(uint32_t x) { return __uint2float_rn(x); }
 B200P_D float Fraction8(uint32_t f8) {
   return __double2float_rn(__dmul_rn(__uint2double_rn(f8), 1e-8));
 }
+B200P_D float Fraction9(uint32_t f9) {
+  return __double2float_rn(__dmul_rn(__uint2double_rn(f9), 1e-9));
+}
 #else
 inline uint32_t Load4(const uint8_t *p) {
   uint32_t a = 0;
@@ -278,6 +281,10 @@ inline int FirstSet(uint32_t x) { return __builtin_ffs(static_cast<int>(x)) - 1;
 inline float U32ToFloat(uint32_t x) { return static_cast<float>(x); }
 inline float Fraction8(uint32_t f8) {
   volatile double q = static_cast<double>(f8) * 1e-8;
+  return static_cast<float>(q);
+}
+inline float Fraction9(uint32_t f9) {
+  volatile double q = static_cast<double>(f9) * 1e-9;
   return static_cast<float>(q);
 }
 #endif
@@ -396,9 +403,19 @@ B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
            byte (f0 & 3) of the third word (the f0 + n2 test below rejects the case where that
            word lies outside the window) */
         n2 = 8u;
-        term = (c >> (8u * (f0 & 3u))) & 0xffu;
-        if (term - '0' < 10u) return false;    /* nine fraction digits and more */
+        const uint32_t k = f0 & 3u;
+        term = (c >> (8u * k)) & 0xffu;
         f8 = Pack4(r1 & 0x0f0f0f0fu, high);
+        if (term - '0' < 10u) {
+          /* a ninth digit ("%.6g" of 0.000123456): F9 * 1e-9 rounds like F9 / 10^9 for every
+             F9 < 10^9 (exhaustive CPU check); rare, so it finishes on its own */
+          if (k == 3u || f0 > 6u) return false;            /* terminator outside the three words */
+          const uint32_t after = (c >> (8u * k + 8u)) & 0xffu;
+          if (after - '0' < 10u || (after | 0x20u) == 'e') return false;   /* ten digits / exponent */
+          v = AddRn(v, Fraction9(f8 * 10u + (term - '0')));
+          *out = negative ? -v : v;
+          return true;
+        }
       }
     }
     if (f0 + n2 > 15u) return false;         /* the terminator must be a real byte of the window */
