@@ -52,6 +52,11 @@ def _random_text(rnd, nlines):
             return "%e" % rnd.uniform(-1e10, 1e10)
         if k < 0.8:
             return rnd.choice(["+1", "1", ".5", "1.", "e", "1e5e3", "1-2", "+", "007"])
+        if k < 0.87:   # the edges of the window fast paths: 7-10 fraction digits, 14-25 digit integers
+            if rnd.random() < 0.5:
+                return "%s%d.%s" % (rnd.choice(["", "", "-"]), rnd.randint(0, 99),
+                                    "".join(rnd.choice("0123456789") for _ in range(rnd.randint(7, 10))))
+            return "".join(rnd.choice("0123456789") for _ in range(rnd.randint(14, 25)))
         return "".join(rnd.choice("0123456789.eE+") for _ in range(rnd.randint(1, 8)))
     seps = [" ", " ", " ", "  ", "\t", ":", ":", " : ", ": ", " :", ",", "|", "qid:", " qid:", "x", "::"]
     eols = ["\n", "\n", "\n", "\r\n", "\r", "\n\n"]
