@@ -7,7 +7,8 @@
  *   CSVParser::ParseBlock            reference src/data/csv_parser.h:63-104
  * and are bit-exact with them (oracle: oracle/dmlc_oracle.c, oracle/_ref).
  *
- * Shape of the computation (HBM-bound byte work, no tensor cores):
+ * Shape of the computation (byte and integer work, no tensor cores; DRAM traffic equals the
+ * algorithmic bytes, the measured limit is instruction issue -- DESIGN.md section 6):
  *
  *   pass 1  WalkText<..., EMIT=false>   count rows / nnz / values / weights / qids per byte range
  *   scan    ScanTiles + ScanFinish      exclusive prefix over ranges -> where each range writes
