@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--chunk-mb", type=int, default=64, help="e2e chunk size (MiB)")
     ap.add_argument("--range-bytes", type=int, default=0)
     ap.add_argument("--depth", type=int, default=3, help="e2e chunks in flight")
+    ap.add_argument("--streams", type=int, default=2,
+                    help="device-resident measurement: handles/streams the windows of a step alternate between")
     ap.add_argument("--host-threads", type=int, default=-1,
                     help="e2e: b200p_set_host_threads (-1 = library default, 0 = copy index[] back)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -278,12 +280,33 @@ def main():
     stream = torch.cuda.current_stream()
     p = Parser("csv", index_bytes=4, label_column=LABEL_COLUMN, device=local,
                range_bytes=args.range_bytes, stream=stream.cuda_stream)
+    # The windows of a step are independent chunks.  With --streams 2 (default) they alternate
+    # between two handles on two streams, so that the last, partly empty wave of one window's
+    # pass 2 is filled by the next window's pass 1 (a 1 000 MB window is 5.2 waves of pass-2 CTAs).
+    # All timing stays on the main stream: the side streams fork from it and join it by events.
+    lanes = [(p, stream)]
+    for _ in range(max(1, args.streams) - 1):
+        side = torch.cuda.Stream()
+        lanes.append((Parser("csv", index_bytes=4, label_column=LABEL_COLUMN, device=local,
+                             range_bytes=args.range_bytes, stream=side.cuda_stream), side))
 
-    def device_step():
-        blk = None
+    def device_step(lanes=lanes):
+        fork = torch.cuda.Event()
+        fork.record(stream)
+        for (_, st) in lanes[1:]:
+            st.wait_event(fork)
+        used = set()
         for j in range(copies):
-            p.parse_device_async(dev.data_ptr() + j * n, n)
-            blk = p.parse_device_finish() if j == copies - 1 else None
+            k = j % len(lanes)
+            lanes[k][0].parse_device_async(dev.data_ptr() + j * n, n)
+            used.add(k)
+        blk = None
+        for k in sorted(used, reverse=True):     # lane 0 (the main stream) last
+            blk = lanes[k][0].parse_device_finish()
+            if k != 0:
+                done = torch.cuda.Event()
+                done.record(lanes[k][1])
+                stream.wait_event(done)
         return blk
 
     # ---------------- device-resident: value --------------------------------------------------
@@ -296,14 +319,14 @@ def main():
     rows = int(blk.rows)
     nnz = int(blk.nnz)
     assert rows == rows_block and nnz == rows * CSV_COLS, (rows, rows_block, nnz)
-    launches0 = p.launch_count()
+    launches0 = sum(q.launch_count() for (q, _) in lanes)
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     for _ in range(args.steps):
         device_step()
     ev1.record(stream)
-    launches = p.launch_count() - launches0     # kernels enqueued inside the timed region
+    launches = sum(q.launch_count() for (q, _) in lanes) - launches0   # kernels enqueued inside the timed region
     barrier()
     # the timed region lasts tens of ms; keep the identical load running (untimed) until
     # nvidia-smi has delivered a few samples
@@ -319,7 +342,7 @@ def main():
     # ---------------- roofline of the dominant kernel (pass 2) ---------------------------------
     p.set_profiling(True)
     for _ in range(2):
-        device_step()
+        device_step(lanes[:1])      # one stream: per-kernel times must not overlap other launches
     torch.cuda.synchronize()
     kt = [p.kernel_time(k) for k in range(3)]
     p.set_profiling(False)
@@ -450,7 +473,8 @@ def main():
                        "text_bytes_per_gpu": text_bytes, "rows_per_gpu": rows * copies,
                        "nnz_per_gpu": nnz * copies, "window_bytes": n,
                        "l2": "inputs (10 GB) far larger than the 126 MB L2; no flush needed",
-                       "parallelism": "shard-per-GPU, no collective"},
+                       "parallelism": "shard-per-GPU, no collective",
+                       "streams": len(lanes)},
             "rows_per_s": world * rows * copies / (dev_ms * 1e-3),
             "gpu_launches": int(launches),
             "clocks": clocks,
@@ -462,7 +486,8 @@ def main():
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line))
-    p.close()
+    for (q, _) in lanes:
+        q.close()
     if world > 1:
         dist.destroy_process_group()
 
