@@ -281,8 +281,8 @@ def main():
     p = Parser("csv", index_bytes=4, label_column=LABEL_COLUMN, device=local,
                range_bytes=args.range_bytes, stream=stream.cuda_stream)
     # The windows of a step are independent chunks.  With --streams 2 (default) they alternate
-    # between two handles on two streams, so that the last, partly empty wave of one window's
-    # pass 2 is filled by the next window's pass 1 (a 1 000 MB window is 5.2 waves of pass-2 CTAs).
+    # between two handles on two streams, so that pass 1 of one window (bound by HBM reads) runs
+    # beside pass 2 of another (bound by instruction issue).
     # All timing stays on the main stream: the side streams fork from it and join it by events.
     lanes = [(p, stream)]
     for _ in range(max(1, args.streams) - 1):
