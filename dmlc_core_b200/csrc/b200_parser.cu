@@ -112,6 +112,7 @@ struct b200p_parser_s {
      held across a wait for a chunk in flight.  err_mu guards `error`, prof_mu one profiling bracket. */
   std::mutex mu, err_mu, prof_mu;
   unsigned long long *d_max; /* two words for b200p_block_max, allocated on first use */
+  std::atomic<bool> saw_qids; /* a LibSVM chunk reported qids: later launches use the QID kernels */
   int host_threads;          /* b200p_set_host_threads; 0 = column ids always come from the GPU */
   HostPool *pool;            /* created on first use */
   std::vector<uint64_t> iota; /* 0, 1, 2, ... in the handle's index width */
@@ -365,7 +366,7 @@ static void Provision(const b200p_handle h, uint64_t nbytes, uint64_t *rows, uin
 
 /* ------------------------------------------------------------------ launches ---------------- */
 template <int FMT, typename IdxT>
-static void LaunchWalks(const WalkParams &p, cudaStream_t s, bool emit) {
+static void LaunchWalks(const WalkParams &p, cudaStream_t s, bool emit, bool qids = false) {
   const unsigned grid = (p.num_ranges + kWarpsPerCta - 1) / kWarpsPerCta;
 #ifdef B200P_CARVEOUT   /* tuning experiments only: shared-memory share of the L1/shared array, percent */
   static bool once = false;
@@ -375,7 +376,13 @@ static void LaunchWalks(const WalkParams &p, cudaStream_t s, bool emit) {
     cudaFuncSetAttribute(WalkText<FMT, IdxT, false>, cudaFuncAttributePreferredSharedMemoryCarveout, B200P_CARVEOUT);
   }
 #endif
-  if (emit) {
+  if (FMT == kLibSVM && qids) {   /* the input has "qid:" on its rows: see TokenGroup */
+    if (emit) {
+      WalkText<FMT, IdxT, true, FMT == kLibSVM><<<grid, kCtaThreads, 0, s>>>(p);
+    } else {
+      WalkText<FMT, IdxT, false, FMT == kLibSVM><<<grid, kCtaThreads, 0, s>>>(p);
+    }
+  } else if (emit) {
     WalkText<FMT, IdxT, true><<<grid, kCtaThreads, 0, s>>>(p);
   } else {
     WalkText<FMT, IdxT, false><<<grid, kCtaThreads, 0, s>>>(p);
@@ -386,7 +393,8 @@ static void LaunchWalk(const b200p_handle h, const WalkParams &p, cudaStream_t s
   const bool wide = h->cfg.index_bytes == 8;
   switch (h->cfg.format) {
     case B200P_FORMAT_LIBSVM:
-      if (wide) LaunchWalks<kLibSVM, uint64_t>(p, s, emit); else LaunchWalks<kLibSVM, uint32_t>(p, s, emit);
+      if (wide) LaunchWalks<kLibSVM, uint64_t>(p, s, emit, h->saw_qids);
+      else LaunchWalks<kLibSVM, uint32_t>(p, s, emit, h->saw_qids);
       break;
     case B200P_FORMAT_LIBFM:
       if (wide) LaunchWalks<kLibFM, uint64_t>(p, s, emit); else LaunchWalks<kLibFM, uint32_t>(p, s, emit);
@@ -503,6 +511,7 @@ static int FinishParse(b200p_handle h, Slot *s) {
     if (rc2 != B200P_OK) return rc2;
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
   }
+  if (sum.total[kQids] != 0) h->saw_qids = true;
   {
     std::lock_guard<std::mutex> g(h->mu);
     h->rows_per_byte = std::max(h->rows_per_byte, static_cast<double>(sum.total[kRows]) / s->nbytes);
@@ -645,6 +654,7 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->rows_per_byte = h->nnz_per_byte = 0.0;
   h->launches = 0;
   h->d_max = NULL;
+  h->saw_qids = false;
   h->pool = NULL;
   h->copied_h2d = h->copied_d2h = 0;
   {

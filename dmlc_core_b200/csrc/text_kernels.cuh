@@ -397,7 +397,7 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
  * of a line positions 1,2 are label, weight (libsvm_parser.h:50-61); everything after that is
  * consumed in groups of 2 (index[:value]) or 3 (field:index[:value]).
  */
-template <int FMT, typename IdxT, bool EMIT>
+template <int FMT, typename IdxT, bool EMIT, bool QID>
 __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &txt,
                                            WarpScratch<FMT> &ws, WalkState<IdxT> &st, uint32_t head,
                                            uint32_t count, int lane) {
@@ -408,6 +408,21 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
 
   const bool general = active && kind == 0u;
   const uint32_t general_m = __ballot_sync(0xffffffffu, general);
+  /* QID instantiation (chosen by the host once a chunk has reported qids): the one longer
+     separator that ranking data has on every row, "<digit-run byte> qid:" (libsvm_parser.h:66-75),
+     is recognised by its six bytes, and a group whose only unusual separators are of that form
+     keeps the mask arithmetic below.  The plain instantiation sends such groups down the general
+     path; both give the same result (the extra registers cost the qid-free shapes 3-4 %, hence
+     two instantiations). */
+  bool qid_number = false;
+  uint32_t qid_numbers = 0u;
+  if (QID && FMT == kLibSVM && general_m != 0u) {
+    if (general && at >= 6u) {
+      qid_number = txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
+                   txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u));
+    }
+    qid_numbers = __ballot_sync(0xffffffffu, qid_number);
+  }
 
   /* role masks of the group (bit i = token i) and the chain context handed to the next group */
   uint32_t m_label, m_weight, m_index, m_value, m_qid = 0u, m_field = 0u;
@@ -417,7 +432,7 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
   bool simple = false;
   uint32_t qid_at = 0;   /* byte after "qid:" when this token follows the probe */
 
-  if (general_m == 0u) {
+  if (general_m == qid_numbers) {
     /* Common case.  With only the three simple separator kinds in the group and no chain longer
        than three tokens, chain positions and roles are plain mask arithmetic on warp-uniform
        ballots -- no per-lane chain walk.  Longer chains and unusual separators take the general
@@ -441,6 +456,12 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
       if (FMT == kLibSVM) {
         m_index = (start_m & ~line_m) | p3;   /* first chain: label, weight, index; else index, value, index */
         m_value = p2 & ~p2f;
+        if (QID) {
+          /* a qid number counts when it follows the label or label:weight; it is read as an
+             index as well (the reference rewinds to it, libsvm_parser.h:74) */
+          m_qid = qid_numbers & (((line_m | p2f) << 1) | (cf & (c1 | c2)));
+          qid_at = at;
+        }
       } else {
         m_field = (start_m & ~line_m) | p3f;  /* field candidates (converted even when dropped) */
         m_index = p2 & ~p2f;                  /* field:index[:value] */
@@ -463,8 +484,9 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
          "<digit-run byte> qid:" (libsvm_parser.h:66-75), is recognised without the walk */
       bool walk = general;
       if (FMT == kLibSVM && general && at >= 6u) {
-        if (txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
-            txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u))) {
+        if (QID ? qid_number
+                : (txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
+                   txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u)))) {
           line_start = false;
           bound = false;            /* first non-blank of the separator is 'q' */
           qid_a = qid_b = true;     /* one space, then "qid:": both probe variants match */
@@ -702,7 +724,7 @@ __device__ __forceinline__ void FieldGroup(const WalkParams &prm, const Text &tx
  * The walk.  grid = ceil(num_ranges / kWarpsPerCta) CTAs of kCtaThreads; warp w of the grid owns
  * byte range [w * range_bytes, (w+1) * range_bytes): the lines whose first byte lies in it.
  */
-template <int FMT, typename IdxT, bool EMIT>
+template <int FMT, typename IdxT, bool EMIT, bool QID = false>
 #ifdef B200P_MIN_CTAS   /* tuning experiments only; the default leaves the register budget to ptxas */
 #define B200P_WALK_BOUNDS __launch_bounds__(kCtaThreads, B200P_MIN_CTAS)
 #else
@@ -919,7 +941,7 @@ __global__ void B200P_WALK_BOUNDS WalkText(const WalkParams prm) {
         if constexpr (FMT == kCSV) {
           FieldGroup<IdxT, EMIT>(prm, txt, ws, st, head, count, lane);
         } else {
-          TokenGroup<FMT, IdxT, EMIT>(prm, txt, ws, st, head, count, lane);
+          TokenGroup<FMT, IdxT, EMIT, QID>(prm, txt, ws, st, head, count, lane);
         }
         head += count;
       }
