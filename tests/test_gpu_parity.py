@@ -364,3 +364,29 @@ def test_one_feeding_and_one_draining_thread(cuda_lib, oracle):
     got["offset"] = np.concatenate(offs)
     got["error"] = 0
     assert same_rowblocks(got, exp) is None
+
+
+def test_csv_with_id_and_timestamp_columns(cuda_lib, oracle):
+    """Integer parts of eight and more digits (ids, epoch seconds, money in cents) leave the window
+    fast path for the general converter: the reference rounds twice per digit once the running
+    value passes 2^24, and so must we."""
+    rnd = random.Random(99)
+    rows = []
+    for i in range(6000):
+        rows.append(",".join([
+            str(rnd.randint(0, 1)),
+            str(1600000000 + rnd.randint(0, 10 ** 8)),                 # epoch seconds
+            "%d.%02d" % (rnd.randint(10 ** 7, 10 ** 11), rnd.randint(0, 99)),
+            "%.6g" % rnd.uniform(-10, 10),
+            "-%d" % rnd.randint(10 ** 8, 10 ** 14),
+            str(rnd.randint(10 ** 14, 10 ** 17)),                      # 15-18 digits: window and general path
+            "%d.%s" % (rnd.randint(10 ** 8, 10 ** 9), "".join(rnd.choice("0123456789") for _ in range(rnd.randint(0, 9)))),
+        ]))
+    text = ("\n".join(rows) + "\n").encode()
+    exp = oracle.parse_buffer("csv", text, 4, 0)
+    assert exp["error"] == 0
+    for rb in (512, 0):
+        p = _parser(cuda_lib, "csv", 4, 0, range_bytes=rb)
+        got = _gpu_result(p, text, "device")
+        p.close()
+        assert same_rowblocks(got, exp) is None, rb

@@ -74,6 +74,13 @@ def test_window_fast_paths_match_oracle(emul, oracle):
                         rnd.choice(["", ".", "." + "".join(rnd.choice("0123456789") for _ in range(rnd.randint(0, 9)))]))
         else:
             toks.append("".join(rnd.choice("0123456789" * 3 + "+-.eE") for _ in range(rnd.randint(1, 20))))
+    # long integer parts (ids, timestamps): eight to sixteen sign + digit bytes, with and without fraction
+    toks += ["16777216", "16777217", "99999999", "123456789", "1609459200", "-1609459200", "+999999999999999",
+             "1234567890123456", "1609459200.5", "123456789.123456", "00000000123", "-0000000012.5"]
+    for _ in range(6000):
+        toks.append(rnd.choice(["", "", "-", "+"]) +
+                    "".join(rnd.choice("0123456789") for _ in range(rnd.randint(7, 16))) +
+                    rnd.choice(["", "", ".", "." + "".join(rnd.choice("0123456789") for _ in range(rnd.randint(1, 8)))]))
     for tok in toks:
         lead = "," * rnd.randint(0, 9)
         tail = rnd.choice(terms) + ("123.5,\n" * rnd.randint(0, 4))
