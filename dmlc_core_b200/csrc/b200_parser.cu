@@ -50,7 +50,8 @@ struct Arrays {
   float *value;
   uint64_t cap_rows;  /* rows the row-sized arrays can hold (offset holds cap_rows + 1) */
   uint64_t cap_nnz;
-  void *block;        /* the one allocation all seven arrays are carved from */
+  unsigned char *narrow; /* LibFM: kNarrowHeader bytes + one byte per field id (see NarrowFields) */
+  void *block;        /* the one allocation all the arrays are carved from */
   Arrays() { std::memset(this, 0, sizeof(*this)); }
 };
 
@@ -325,18 +326,19 @@ static int EnsureArrays(b200p_handle h, Arrays *a, uint64_t rows, uint64_t nnz, 
   const bool has_weight = fmt != B200P_FORMAT_CSV, has_qid = fmt == B200P_FORMAT_LIBSVM;
   const bool has_field = fmt == B200P_FORMAT_LIBFM;
   const auto pad = [](uint64_t bytes) { return (bytes + 255) / 256 * 256; };
-  const uint64_t sizes[7] = {pad((cap_rows + 1) * 8), pad(cap_rows * 4), has_weight ? pad(cap_rows * 4) : 0,
+  const uint64_t sizes[8] = {pad((cap_rows + 1) * 8), pad(cap_rows * 4), has_weight ? pad(cap_rows * 4) : 0,
                              has_qid ? pad(cap_rows * 8) : 0, has_field ? pad(cap_nnz * iw) : 0,
-                             pad(cap_nnz * iw), pad(cap_nnz * 4)};
+                             pad(cap_nnz * iw), pad(cap_nnz * 4),
+                             has_field ? pad(kNarrowHeader + cap_nnz) : 0};
   uint64_t total = 0;
-  for (int i = 0; i < 7; ++i) total += sizes[i];
+  for (int i = 0; i < 8; ++i) total += sizes[i];
   if (pinned) PinnedFree(a->block); else cudaFree(a->block);
   *a = Arrays();
   void *block = NULL;
   CUDA_TRY(h, pinned ? PinnedAlloc(&block, total) : DeviceAlloc(&block, total));
   char *at = static_cast<char *>(block);
-  void *parts[7];
-  for (int i = 0; i < 7; ++i) {
+  void *parts[8];
+  for (int i = 0; i < 8; ++i) {
     parts[i] = sizes[i] != 0 ? at : NULL;
     at += sizes[i];
   }
@@ -348,6 +350,7 @@ static int EnsureArrays(b200p_handle h, Arrays *a, uint64_t rows, uint64_t nnz, 
   a->field = parts[4];
   a->index = parts[5];
   a->value = static_cast<float *>(parts[6]);
+  a->narrow = static_cast<unsigned char *>(parts[7]);
   a->cap_rows = cap_rows;
   a->cap_nnz = cap_nnz;
   return B200P_OK;
@@ -607,6 +610,25 @@ static void RebuildCsvIndex(b200p_handle h, Slot *s, uint64_t rows) {
     } else {
       CsvColumnIds(offset, r0, r1, static_cast<uint32_t *>(index),
                    reinterpret_cast<const uint32_t *>(iota), kIota);
+    }
+  });
+}
+
+/* host.field of a LibFM chunk from the one-byte ids in host.narrow, spread over the pool */
+static void WidenFields(b200p_handle h, Slot *s, uint64_t nnz) {
+  if (h->pool == NULL) h->pool = new HostPool(h->host_threads);
+  const int parts = static_cast<int>(std::min<uint64_t>((nnz + 65535) / 65536, 4ull * h->pool->threads()));
+  const unsigned char *from = s->host.narrow + kNarrowHeader;
+  void *to = s->host.field;
+  const bool wide = h->cfg.index_bytes == 8;
+  h->pool->Run(parts, [=](int part) {
+    const uint64_t lo = nnz * part / parts, hi = nnz * (part + 1) / parts;
+    if (wide) {
+      uint64_t *dst = static_cast<uint64_t *>(to);
+      for (uint64_t i = lo; i < hi; ++i) dst[i] = from[i];
+    } else {
+      uint32_t *dst = static_cast<uint32_t *>(to);
+      for (uint64_t i = lo; i < hi; ++i) dst[i] = from[i];
     }
   });
 }
@@ -975,14 +997,32 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
          entries on average are cheaper to copy than to rebuild row by row. */
       const bool rebuild = h->cfg.format == B200P_FORMAT_CSV && h->host_threads > 0 &&
                            nnz >= 16 * rows;
+      /* LibFM field ids cross the link as one byte each and are widened to IndexType by the same
+         host threads (NarrowFields); an id above 255 anywhere in the chunk brings the wide array
+         over after all. */
+      const bool narrow = h->cfg.format == B200P_FORMAT_LIBFM && h->host_threads > 0 && nnz >= 4096;
       uint64_t bytes = (rows + 1) * 8 + rows * 4;
-      CUDA_TRY(h, cudaMemcpyAsync(s->host.offset, s->dev.offset, (rows + 1) * 8, cudaMemcpyDeviceToHost, st));
-      if (rebuild) {
+      if (rebuild || narrow) {
         if (s->offsets_home == NULL) {
           CUDA_TRY(h, cudaEventCreateWithFlags(&s->offsets_home, cudaEventDisableTiming));
         }
-        CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
       }
+      if (narrow) {
+        CUDA_TRY(h, cudaMemsetAsync(s->dev.narrow, 0, 4, st));
+        const unsigned grid = static_cast<unsigned>(std::min<uint64_t>((nnz + 255) / 256, 148 * 8));
+        if (iw == 8) {
+          NarrowFields<uint64_t><<<grid, 256, 0, st>>>(static_cast<const uint64_t *>(s->dev.field), nnz, s->dev.narrow);
+        } else {
+          NarrowFields<uint32_t><<<grid, 256, 0, st>>>(static_cast<const uint32_t *>(s->dev.field), nnz, s->dev.narrow);
+        }
+        ++h->launches;
+        CUDA_TRY(h, cudaGetLastError());
+        CUDA_TRY(h, cudaMemcpyAsync(s->host.narrow, s->dev.narrow, kNarrowHeader + nnz, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
+        bytes += kNarrowHeader + nnz;
+      }
+      CUDA_TRY(h, cudaMemcpyAsync(s->host.offset, s->dev.offset, (rows + 1) * 8, cudaMemcpyDeviceToHost, st));
+      if (rebuild) CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
       CUDA_TRY(h, cudaMemcpyAsync(s->host.label, s->dev.label, rows * 4, cudaMemcpyDeviceToHost, st));
       if (sum.total[kWeights] != 0) {
         CUDA_TRY(h, cudaMemcpyAsync(s->host.weight, s->dev.weight, sum.total[kWeights] * 4, cudaMemcpyDeviceToHost, st));
@@ -997,7 +1037,7 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
           CUDA_TRY(h, cudaMemcpyAsync(s->host.index, s->dev.index, nnz * iw, cudaMemcpyDeviceToHost, st));
           bytes += nnz * iw;
         }
-        if (h->cfg.format == B200P_FORMAT_LIBFM) {
+        if (h->cfg.format == B200P_FORMAT_LIBFM && !narrow) {
           CUDA_TRY(h, cudaMemcpyAsync(s->host.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
           bytes += nnz * iw;
         }
@@ -1009,6 +1049,17 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
       if (rebuild) {
         CUDA_TRY(h, cudaEventSynchronize(s->offsets_home));
         RebuildCsvIndex(h, s, rows);
+      }
+      if (narrow) {
+        CUDA_TRY(h, cudaEventSynchronize(s->offsets_home));
+        unsigned int overflow = 0;
+        std::memcpy(&overflow, s->host.narrow, sizeof(overflow));
+        if (overflow != 0u) {
+          CUDA_TRY(h, cudaMemcpyAsync(s->host.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
+          bytes += nnz * iw;
+        } else {
+          WidenFields(h, s, nnz);
+        }
       }
       CUDA_TRY(h, cudaStreamSynchronize(st));
       h->copied_d2h += bytes;

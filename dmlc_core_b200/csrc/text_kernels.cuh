@@ -1093,5 +1093,26 @@ __global__ void __launch_bounds__(256) MaxOfArray(const IdxT *values, unsigned l
   }
 }
 
+/*
+ * LibFM field ids for the trip over PCIe: one byte each behind a 256-byte header whose first
+ * word is set when some id does not fit (b200p_next then copies the wide array after all).
+ * Field ids are small by nature (the reference's own test data has 39); as IndexType they are 4
+ * or 8 bytes of every entry sent back to the host.
+ */
+constexpr unsigned kNarrowHeader = 256;
+template <typename IdxT>
+__global__ void __launch_bounds__(256) NarrowFields(const IdxT *field, unsigned long long n,
+                                                    unsigned char *narrow) {
+  bool wide = false;
+  for (unsigned long long i = blockIdx.x * 256ull + threadIdx.x; i < n; i += gridDim.x * 256ull) {
+    const IdxT v = field[i];
+    narrow[kNarrowHeader + i] = static_cast<unsigned char>(v);
+    wide = wide || v > static_cast<IdxT>(255);
+  }
+  if (__any_sync(0xffffffffu, wide) && (threadIdx.x & 31) == 0) {
+    atomicOr(reinterpret_cast<unsigned int *>(narrow), 1u);
+  }
+}
+
 }  // namespace b200p
 #endif  // DMLC_CORE_B200_TEXT_KERNELS_CUH_

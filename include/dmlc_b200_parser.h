@@ -139,7 +139,9 @@ int b200p_pending(b200p_handle h);
  * or more entries, index[] is not copied back from the GPU -- it is implied by offset[] (the j-th
  * non-label field of a row has column id j, src/data/csv_parser.h:84-88) -- but written into the
  * pinned result by these threads while value[] is still on the link; that halves the
- * device-to-host bytes of the path. 0 = always copy index[] from the GPU. Default: a quarter of
+ * device-to-host bytes of the path. The same threads widen LibFM field ids, which cross the
+ * link as one byte each when every id of the chunk is below 256. 0 = always copy the full arrays
+ * from the GPU. Default: a quarter of
  * the host's cores (divided by LOCAL_WORLD_SIZE when a launcher exports it), at most 4; the
  * environment variable B200P_HOST_THREADS overrides the default.
  * The arrays returned are identical either way. No reference counterpart.

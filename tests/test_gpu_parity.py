@@ -390,3 +390,38 @@ def test_csv_with_id_and_timestamp_columns(cuda_lib, oracle):
         got = _gpu_result(p, text, "device")
         p.close()
         assert same_rowblocks(got, exp) is None, rb
+
+
+@pytest.mark.parametrize("ib", [4, 8])
+def test_libfm_field_ids_cross_the_link_as_bytes(cuda_lib, oracle, ib):
+    """b200p_next brings LibFM field ids back as one byte each and widens them on the host; a chunk
+    with an id above 255 falls back to the wide copy.  Same arrays either way, fewer bytes moved."""
+    rnd = random.Random(31)
+
+    def rows(n, max_field):
+        out = []
+        for _ in range(n):
+            out.append("%d " % rnd.randint(0, 1) + " ".join(
+                "%d:%d:%.4g" % (rnd.randint(0, max_field), rnd.randint(0, 10 ** 9), rnd.random())
+                for _ in range(rnd.randint(5, 40))))
+        return ("\n".join(out) + "\n").encode()
+
+    small, large = rows(4000, 255), rows(4000, 70000)      # second chunk overflows a byte
+    exp = [oracle.parse_buffer("libfm", c, ib) for c in (small, large, small)]
+    moved = {}
+    for threads in (0, 4):
+        p = _parser(cuda_lib, "libfm", ib, -1, chunk_bytes=4 << 20, depth=2)
+        p.set_host_threads(threads)
+        got = []
+        for c in (small, large, small):
+            p.submit(c)
+            got.append(p.next())
+        moved[threads] = p.copied_bytes()[1]
+        p.close()
+        for g, e in zip(got, exp):
+            g["error"] = 0
+            assert same_rowblocks(g, e) is None, threads
+    nnz_small = len(exp[0]["index"])
+    saved = moved[0] - moved[4]
+    # two small chunks save (ib - 1) bytes per entry minus the header; the large one costs its narrow copy
+    assert saved == 2 * (nnz_small * (ib - 1) - 256) - (len(exp[1]["index"]) + 256)
