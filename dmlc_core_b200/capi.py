@@ -24,7 +24,8 @@ EXPORTS = (
     "b200p_create", "b200p_destroy", "b200p_last_error", "b200p_parse_device",
     "b200p_parse_device_async", "b200p_parse_device_finish", "b200p_input_buffer",
     "b200p_submit", "b200p_next", "b200p_pending", "b200p_fetch", "b200p_launch_count",
-    "b200p_set_host_threads", "b200p_copied_bytes",
+    "b200p_set_host_threads", "b200p_copied_bytes", "b200p_next_to", "b200p_host_alloc",
+    "b200p_host_free",
     "b200p_set_profiling", "b200p_kernel_time", "b200p_version", "b200p_parse_device_noalloc",
     "b200p_block_max",
 )
@@ -47,6 +48,14 @@ class RowBlock(C.Structure):
                 ("qid", C.c_void_p), ("field", C.c_void_p), ("index", C.c_void_p),
                 ("value", C.c_void_p), ("text_bytes", C.c_uint64), ("index_bytes", C.c_int32),
                 ("on_device", C.c_int32)]
+
+
+class Destination(C.Structure):
+    """b200p_destination: caller-owned host arrays for b200p_next_to."""
+    _fields_ = [("offset", C.c_void_p), ("label", C.c_void_p), ("weight", C.c_void_p),
+                ("qid", C.c_void_p), ("field", C.c_void_p), ("index", C.c_void_p),
+                ("value", C.c_void_p), ("cap_rows", C.c_uint64), ("cap_nnz", C.c_uint64),
+                ("offset_base", C.c_uint64)]
 
 
 class NoAllocRequest(C.Structure):
@@ -93,6 +102,12 @@ def load():
     lib.b200p_pending.restype = C.c_int
     lib.b200p_fetch.argtypes = [H, C.c_void_p, C.c_void_p, C.c_uint64]
     lib.b200p_fetch.restype = C.c_int
+    lib.b200p_next_to.argtypes = [H, C.POINTER(Destination), C.POINTER(RowBlock)]
+    lib.b200p_next_to.restype = C.c_int
+    lib.b200p_host_alloc.argtypes = [H, C.c_uint64, C.POINTER(C.c_void_p)]
+    lib.b200p_host_alloc.restype = C.c_int
+    lib.b200p_host_free.argtypes = [C.c_void_p]
+    lib.b200p_host_free.restype = None
     lib.b200p_set_host_threads.argtypes = [H, C.c_int]
     lib.b200p_set_host_threads.restype = C.c_int
     lib.b200p_copied_bytes.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -260,6 +275,23 @@ class Parser(object):
 
     def launch_count(self):
         return int(self.lib.b200p_launch_count(self.handle))
+
+    def host_alloc(self, nbytes):
+        """Pinned, huge-page backed host memory (address); release with host_free()."""
+        ptr = C.c_void_p()
+        self._check(self.lib.b200p_host_alloc(self.handle, int(nbytes), C.byref(ptr)))
+        return ptr.value
+
+    def host_free(self, ptr):
+        self.lib.b200p_host_free(ptr)
+
+    def next_to(self, dest):
+        """b200p_next_to: (rc, RowBlock); rc is E_CAPACITY (6) when the block stays queued."""
+        blk = RowBlock()
+        rc = self.lib.b200p_next_to(self.handle, C.byref(dest), C.byref(blk))
+        if rc not in (0, 6):
+            self._check(rc)
+        return rc, blk
 
     def set_host_threads(self, threads):
         """Host threads that rebuild CSV column ids in next(); 0 = always copy them from the GPU."""

@@ -71,6 +71,8 @@ struct Slot {
   uint64_t nbytes;
   bool busy;
   cudaEvent_t offsets_home; /* streaming path: offset[] has reached the host (created on first use) */
+  unsigned char *h_narrow;  /* pinned landing place of the one-byte LibFM field ids */
+  uint64_t narrow_cap;
   Slot() { std::memset(this, 0, sizeof(*this)); }
 };
 
@@ -211,7 +213,11 @@ static int Fail(b200p_handle h, int code, const char *msg) {
  */
 namespace {
 std::mutex g_registered_mu;
-std::vector<void *> g_registered;   /* blocks obtained through the register path */
+struct Registered {
+  void *ptr;
+  int device;   /* current when the block was pinned; made current again to unpin it */
+};
+std::vector<Registered> g_registered;   /* blocks obtained through the register path */
 
 bool HugePagesOnOffer() {
   static const bool on = [] {
@@ -275,8 +281,10 @@ static cudaError_t PinnedAlloc(void **out, uint64_t bytes) {
         for (std::thread &th : crew) th.join();
       }
       if (cudaHostRegister(p, rounded, cudaHostRegisterPortable) == cudaSuccess) {
+        Registered r = {p, 0};
+        if (cudaGetDevice(&r.device) != cudaSuccess) r.device = 0;
         std::lock_guard<std::mutex> g(g_registered_mu);
-        g_registered.push_back(p);
+        g_registered.push_back(r);
         *out = p;
         return cudaSuccess;
       }
@@ -289,16 +297,26 @@ static cudaError_t PinnedAlloc(void **out, uint64_t bytes) {
 
 static void PinnedFree(void *p) {
   if (p == NULL) return;
+  int device = -1;
   {
     std::lock_guard<std::mutex> g(g_registered_mu);
-    std::vector<void *>::iterator it = std::find(g_registered.begin(), g_registered.end(), p);
-    if (it == g_registered.end()) {
-      cudaFreeHost(p);
-      return;
+    for (size_t i = 0; i < g_registered.size(); ++i) {
+      if (g_registered[i].ptr == p) {
+        device = g_registered[i].device;
+        g_registered.erase(g_registered.begin() + static_cast<long>(i));
+        break;
+      }
     }
-    g_registered.erase(it);
   }
+  if (device < 0) {
+    cudaFreeHost(p);
+    return;
+  }
+  int current = -1;
+  if (cudaGetDevice(&current) != cudaSuccess) current = -1;
+  if (current != device) cudaSetDevice(device);
   cudaHostUnregister(p);
+  if (current >= 0 && current != device) cudaSetDevice(current);
   std::free(p);
 }
 
@@ -329,7 +347,7 @@ static int EnsureArrays(b200p_handle h, Arrays *a, uint64_t rows, uint64_t nnz, 
   const uint64_t sizes[8] = {pad((cap_rows + 1) * 8), pad(cap_rows * 4), has_weight ? pad(cap_rows * 4) : 0,
                              has_qid ? pad(cap_rows * 8) : 0, has_field ? pad(cap_nnz * iw) : 0,
                              pad(cap_nnz * iw), pad(cap_nnz * 4),
-                             has_field ? pad(kNarrowHeader + cap_nnz) : 0};
+                             has_field && !pinned ? pad(kNarrowHeader + cap_nnz) : 0};
   uint64_t total = 0;
   for (int i = 0; i < 8; ++i) total += sizes[i];
   if (pinned) PinnedFree(a->block); else cudaFree(a->block);
@@ -560,6 +578,7 @@ static void FillBlock(const b200p_handle h, const Slot &s, const Arrays &a, bool
 static void DestroySlot(Slot *s) {
   if (s->stream != NULL) cudaStreamSynchronize(s->stream);
   PinnedFree(s->h_text);
+  PinnedFree(s->h_narrow);
   cudaFree(s->d_text);
   cudaFree(s->d_counts);
   cudaFree(s->d_summary);
@@ -586,7 +605,7 @@ static int InitSlot(b200p_handle h, Slot *s, cudaStream_t stream) {
 }
 
 /* host.index of a CSV chunk from host.offset (already on the host), spread over the pool */
-static void RebuildCsvIndex(b200p_handle h, Slot *s, uint64_t rows) {
+static void RebuildCsvIndex(b200p_handle h, const Arrays &to, uint64_t rows) {
   const bool wide = h->cfg.index_bytes == 8;
   const uint64_t kIota = 4096;
   if (h->iota.empty()) {
@@ -600,8 +619,8 @@ static void RebuildCsvIndex(b200p_handle h, Slot *s, uint64_t rows) {
   }
   if (h->pool == NULL) h->pool = new HostPool(h->host_threads);
   const int parts = static_cast<int>(std::min<uint64_t>(rows, 4ull * h->pool->threads()));
-  const unsigned long long *offset = s->host.offset;
-  void *index = s->host.index;
+  const unsigned long long *offset = to.offset;
+  void *index = to.index;
   const uint64_t *iota = h->iota.data();
   h->pool->Run(parts, [=](int part) {
     const uint64_t r0 = rows * part / parts, r1 = rows * (part + 1) / parts;
@@ -615,11 +634,11 @@ static void RebuildCsvIndex(b200p_handle h, Slot *s, uint64_t rows) {
 }
 
 /* host.field of a LibFM chunk from the one-byte ids in host.narrow, spread over the pool */
-static void WidenFields(b200p_handle h, Slot *s, uint64_t nnz) {
+static void WidenFields(b200p_handle h, const Slot *s, const Arrays &dest, uint64_t nnz) {
   if (h->pool == NULL) h->pool = new HostPool(h->host_threads);
   const int parts = static_cast<int>(std::min<uint64_t>((nnz + 65535) / 65536, 4ull * h->pool->threads()));
-  const unsigned char *from = s->host.narrow + kNarrowHeader;
-  void *to = s->host.field;
+  const unsigned char *from = s->h_narrow + kNarrowHeader;
+  void *to = dest.field;
   const bool wide = h->cfg.index_bytes == 8;
   h->pool->Run(parts, [=](int part) {
     const uint64_t lo = nnz * part / parts, hi = nnz * (part + 1) / parts;
@@ -963,6 +982,107 @@ int b200p_pending(b200p_handle h) {
   return static_cast<int>(h->in_flight.size());
 }
 
+/*
+ * The finished chunk of slot `s` into the host arrays `to` (the slot's own pinned mirrors for
+ * b200p_next, the caller's memory for b200p_next_to): copies, the host-side rebuild of CSV
+ * column ids / LibFM field ids, and a final synchronisation.  `base` is added to every offset.
+ */
+static int DeliverBlock(b200p_handle h, Slot *s, const Arrays &to, uint64_t base) {
+  const ChunkSummary &sum = *s->h_summary;
+  const uint64_t rows = sum.total[kRows], nnz = sum.total[kNnz];
+  {
+    const size_t iw = h->cfg.index_bytes;
+    cudaStream_t st = s->stream;
+    if (rows != 0) {
+      /* Wide CSV rows: index[] is fully determined by offset[] (the j-th non-label field of a row
+         has column id j, csv_parser.h:84-88), so those nnz * index_bytes bytes are not brought
+         back over PCIe -- about half of this path's device-to-host traffic -- but written by a
+         few host threads while the value[] copy is still on the link.  Rows shorter than 16
+         entries on average are cheaper to copy than to rebuild row by row. */
+      const bool rebuild = h->cfg.format == B200P_FORMAT_CSV && h->host_threads > 0 &&
+                           nnz >= 16 * rows;
+      /* LibFM field ids cross the link as one byte each and are widened to IndexType by the same
+         host threads (NarrowFields); an id above 255 anywhere in the chunk brings the wide array
+         over after all. */
+      const bool narrow = h->cfg.format == B200P_FORMAT_LIBFM && h->host_threads > 0 && nnz >= 4096;
+      uint64_t bytes = (rows + 1) * 8 + rows * 4;
+      if (rebuild || narrow) {
+        if (s->offsets_home == NULL) {
+          CUDA_TRY(h, cudaEventCreateWithFlags(&s->offsets_home, cudaEventDisableTiming));
+        }
+      }
+      if (narrow) {
+        if (kNarrowHeader + nnz > s->narrow_cap) {
+          PinnedFree(s->h_narrow);
+          s->h_narrow = NULL;
+          s->narrow_cap = 0;
+          const uint64_t cap = kNarrowHeader + nnz + nnz / 4;
+          CUDA_TRY(h, PinnedAlloc(reinterpret_cast<void **>(&s->h_narrow), cap));
+          s->narrow_cap = cap;
+        }
+        CUDA_TRY(h, cudaMemsetAsync(s->dev.narrow, 0, 4, st));
+        const unsigned grid = static_cast<unsigned>(std::min<uint64_t>((nnz + 255) / 256, 148 * 8));
+        if (iw == 8) {
+          NarrowFields<uint64_t><<<grid, 256, 0, st>>>(static_cast<const uint64_t *>(s->dev.field), nnz, s->dev.narrow);
+        } else {
+          NarrowFields<uint32_t><<<grid, 256, 0, st>>>(static_cast<const uint32_t *>(s->dev.field), nnz, s->dev.narrow);
+        }
+        ++h->launches;
+        CUDA_TRY(h, cudaGetLastError());
+        CUDA_TRY(h, cudaMemcpyAsync(s->h_narrow, s->dev.narrow, kNarrowHeader + nnz, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
+        bytes += kNarrowHeader + nnz;
+      }
+      CUDA_TRY(h, cudaMemcpyAsync(to.offset, s->dev.offset, (rows + 1) * 8, cudaMemcpyDeviceToHost, st));
+      if (rebuild) CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
+      CUDA_TRY(h, cudaMemcpyAsync(to.label, s->dev.label, rows * 4, cudaMemcpyDeviceToHost, st));
+      if (sum.total[kWeights] != 0) {
+        CUDA_TRY(h, cudaMemcpyAsync(to.weight, s->dev.weight, sum.total[kWeights] * 4, cudaMemcpyDeviceToHost, st));
+        bytes += sum.total[kWeights] * 4;
+      }
+      if (sum.total[kQids] != 0) {
+        CUDA_TRY(h, cudaMemcpyAsync(to.qid, s->dev.qid, sum.total[kQids] * 8, cudaMemcpyDeviceToHost, st));
+        bytes += sum.total[kQids] * 8;
+      }
+      if (nnz != 0) {
+        if (!rebuild) {
+          CUDA_TRY(h, cudaMemcpyAsync(to.index, s->dev.index, nnz * iw, cudaMemcpyDeviceToHost, st));
+          bytes += nnz * iw;
+        }
+        if (h->cfg.format == B200P_FORMAT_LIBFM && !narrow) {
+          CUDA_TRY(h, cudaMemcpyAsync(to.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
+          bytes += nnz * iw;
+        }
+      }
+      if (sum.total[kValues] != 0) {
+        CUDA_TRY(h, cudaMemcpyAsync(to.value, s->dev.value, sum.total[kValues] * 4, cudaMemcpyDeviceToHost, st));
+        bytes += sum.total[kValues] * 4;
+      }
+      if (rebuild) {
+        CUDA_TRY(h, cudaEventSynchronize(s->offsets_home));
+        RebuildCsvIndex(h, to, rows);
+      }
+      if (narrow) {
+        CUDA_TRY(h, cudaEventSynchronize(s->offsets_home));
+        unsigned int overflow = 0;
+        std::memcpy(&overflow, s->h_narrow, sizeof(overflow));
+        if (overflow != 0u) {
+          CUDA_TRY(h, cudaMemcpyAsync(to.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
+          bytes += nnz * iw;
+        } else {
+          WidenFields(h, s, to, nnz);
+        }
+      }
+      CUDA_TRY(h, cudaStreamSynchronize(st));
+      h->copied_d2h += bytes;
+    }
+    if (base != 0 && rows != 0) {
+      for (uint64_t i = 0; i <= rows; ++i) to.offset[i] += base;
+    }
+  }
+  return B200P_OK;
+}
+
 int b200p_next(b200p_handle h, b200p_rowblock *out) {
   if (h == NULL || out == NULL) return B200P_E_INVALID;
   DeviceScope on_device(h->cfg.device);
@@ -987,88 +1107,78 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
     const uint64_t rows = sum.total[kRows], nnz = sum.total[kNnz];
     rc = EnsureArrays(h, &s->host, rows, nnz, true);
     if (rc != B200P_OK) return rc;
-    const size_t iw = h->cfg.index_bytes;
-    cudaStream_t st = s->stream;
-    if (rows != 0) {
-      /* Wide CSV rows: index[] is fully determined by offset[] (the j-th non-label field of a row
-         has column id j, csv_parser.h:84-88), so those nnz * index_bytes bytes are not brought
-         back over PCIe -- about half of this path's device-to-host traffic -- but written by a
-         few host threads while the value[] copy is still on the link.  Rows shorter than 16
-         entries on average are cheaper to copy than to rebuild row by row. */
-      const bool rebuild = h->cfg.format == B200P_FORMAT_CSV && h->host_threads > 0 &&
-                           nnz >= 16 * rows;
-      /* LibFM field ids cross the link as one byte each and are widened to IndexType by the same
-         host threads (NarrowFields); an id above 255 anywhere in the chunk brings the wide array
-         over after all. */
-      const bool narrow = h->cfg.format == B200P_FORMAT_LIBFM && h->host_threads > 0 && nnz >= 4096;
-      uint64_t bytes = (rows + 1) * 8 + rows * 4;
-      if (rebuild || narrow) {
-        if (s->offsets_home == NULL) {
-          CUDA_TRY(h, cudaEventCreateWithFlags(&s->offsets_home, cudaEventDisableTiming));
-        }
-      }
-      if (narrow) {
-        CUDA_TRY(h, cudaMemsetAsync(s->dev.narrow, 0, 4, st));
-        const unsigned grid = static_cast<unsigned>(std::min<uint64_t>((nnz + 255) / 256, 148 * 8));
-        if (iw == 8) {
-          NarrowFields<uint64_t><<<grid, 256, 0, st>>>(static_cast<const uint64_t *>(s->dev.field), nnz, s->dev.narrow);
-        } else {
-          NarrowFields<uint32_t><<<grid, 256, 0, st>>>(static_cast<const uint32_t *>(s->dev.field), nnz, s->dev.narrow);
-        }
-        ++h->launches;
-        CUDA_TRY(h, cudaGetLastError());
-        CUDA_TRY(h, cudaMemcpyAsync(s->host.narrow, s->dev.narrow, kNarrowHeader + nnz, cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
-        bytes += kNarrowHeader + nnz;
-      }
-      CUDA_TRY(h, cudaMemcpyAsync(s->host.offset, s->dev.offset, (rows + 1) * 8, cudaMemcpyDeviceToHost, st));
-      if (rebuild) CUDA_TRY(h, cudaEventRecord(s->offsets_home, st));
-      CUDA_TRY(h, cudaMemcpyAsync(s->host.label, s->dev.label, rows * 4, cudaMemcpyDeviceToHost, st));
-      if (sum.total[kWeights] != 0) {
-        CUDA_TRY(h, cudaMemcpyAsync(s->host.weight, s->dev.weight, sum.total[kWeights] * 4, cudaMemcpyDeviceToHost, st));
-        bytes += sum.total[kWeights] * 4;
-      }
-      if (sum.total[kQids] != 0) {
-        CUDA_TRY(h, cudaMemcpyAsync(s->host.qid, s->dev.qid, sum.total[kQids] * 8, cudaMemcpyDeviceToHost, st));
-        bytes += sum.total[kQids] * 8;
-      }
-      if (nnz != 0) {
-        if (!rebuild) {
-          CUDA_TRY(h, cudaMemcpyAsync(s->host.index, s->dev.index, nnz * iw, cudaMemcpyDeviceToHost, st));
-          bytes += nnz * iw;
-        }
-        if (h->cfg.format == B200P_FORMAT_LIBFM && !narrow) {
-          CUDA_TRY(h, cudaMemcpyAsync(s->host.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
-          bytes += nnz * iw;
-        }
-      }
-      if (sum.total[kValues] != 0) {
-        CUDA_TRY(h, cudaMemcpyAsync(s->host.value, s->dev.value, sum.total[kValues] * 4, cudaMemcpyDeviceToHost, st));
-        bytes += sum.total[kValues] * 4;
-      }
-      if (rebuild) {
-        CUDA_TRY(h, cudaEventSynchronize(s->offsets_home));
-        RebuildCsvIndex(h, s, rows);
-      }
-      if (narrow) {
-        CUDA_TRY(h, cudaEventSynchronize(s->offsets_home));
-        unsigned int overflow = 0;
-        std::memcpy(&overflow, s->host.narrow, sizeof(overflow));
-        if (overflow != 0u) {
-          CUDA_TRY(h, cudaMemcpyAsync(s->host.field, s->dev.field, nnz * iw, cudaMemcpyDeviceToHost, st));
-          bytes += nnz * iw;
-        } else {
-          WidenFields(h, s, nnz);
-        }
-      }
-      CUDA_TRY(h, cudaStreamSynchronize(st));
-      h->copied_d2h += bytes;
-    }
+    rc = DeliverBlock(h, s, s->host, 0);
+    if (rc != B200P_OK) return rc;
   }
   FillBlock(h, *s, s->host, false, out);
   h->last_block = s;
   return B200P_OK;
 }
+
+int b200p_next_to(b200p_handle h, const b200p_destination *dst, b200p_rowblock *out) {
+  if (h == NULL || dst == NULL || out == NULL) return B200P_E_INVALID;
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
+  Slot *s = NULL;
+  int id = -1;
+  {
+    std::lock_guard<std::mutex> g(h->mu);
+    if (h->in_flight.empty()) return Fail(h, B200P_E_EMPTY, "b200p_next_to: nothing submitted");
+    id = h->in_flight.front();   /* stays queued until it is known to fit: only this thread pops */
+    s = &h->slots[id];
+  }
+  int rc = FinishParse(h, s);
+  std::memset(out, 0, sizeof(*out));
+  if (rc == B200P_OK && s->nbytes != 0) {
+    const ChunkSummary &sum = *s->h_summary;
+    out->rows = sum.total[kRows];
+    out->nnz = sum.total[kNnz];
+    if (sum.total[kRows] > dst->cap_rows || sum.total[kNnz] > dst->cap_nnz) {
+      return Fail(h, B200P_E_CAPACITY, "b200p_next_to: the destination arrays are too small for the next block; "
+                                       "it stays queued (rows and nnz say how much room it needs)");
+    }
+  }
+  {
+    std::lock_guard<std::mutex> g(h->mu);
+    h->in_flight.pop_front();
+    s->busy = false;
+    h->returned_slot = -1;     /* nothing of any slot is lent out: the arrays are the caller's */
+    h->last_block = NULL;
+  }
+  if (rc != B200P_OK) return rc;
+  Arrays to;
+  to.offset = reinterpret_cast<unsigned long long *>(dst->offset);
+  to.label = dst->label;
+  to.weight = dst->weight;
+  to.qid = reinterpret_cast<unsigned long long *>(dst->qid);
+  to.field = dst->field;
+  to.index = dst->index;
+  to.value = dst->value;
+  if (s->nbytes != 0) {
+    const ChunkSummary &sum = *s->h_summary;
+    if ((sum.total[kRows] != 0 && (to.offset == NULL || to.label == NULL)) ||
+        (sum.total[kNnz] != 0 && to.index == NULL) || (sum.total[kValues] != 0 && to.value == NULL) ||
+        (sum.total[kWeights] != 0 && to.weight == NULL) || (sum.total[kQids] != 0 && to.qid == NULL) ||
+        (h->cfg.format == B200P_FORMAT_LIBFM && sum.total[kNnz] != 0 && to.field == NULL)) {
+      return Fail(h, B200P_E_INVALID, "b200p_next_to: a destination array this block needs is NULL");
+    }
+    rc = DeliverBlock(h, s, to, dst->offset_base);
+    if (rc != B200P_OK) return rc;
+  }
+  FillBlock(h, *s, to, false, out);
+  h->last_block = s;           /* b200p_block_max still works: the device arrays are intact */
+  return B200P_OK;
+}
+
+int b200p_host_alloc(b200p_handle h, uint64_t bytes, void **ptr) {
+  if (h == NULL || ptr == NULL) return B200P_E_INVALID;
+  DeviceScope on_device(h->cfg.device);
+  CUDA_TRY(h, on_device.status());
+  CUDA_TRY(h, PinnedAlloc(ptr, bytes));
+  return B200P_OK;
+}
+
+void b200p_host_free(void *ptr) { PinnedFree(ptr); }
 
 
 /* ------------------------------------------------------------------------------------------

@@ -135,6 +135,37 @@ int b200p_next(b200p_handle h, b200p_rowblock *out);
 int b200p_pending(b200p_handle h);
 
 /*
+ * b200p_next with the arrays written straight into memory of the caller's choosing, at the
+ * caller's running position: what RowBlockContainer::Push(RowBlock) does for BasicRowIter
+ * (src/data/row_block.h:122-166, src/data/basic_row_iter.h:62-82) without the intermediate block
+ * and its memcpy. offset receives rows + 1 entries, each increased by offset_base (so that the
+ * first one overwrites the previous block's last entry with the same value); the other arrays
+ * receive exactly the counts reported in *out. Absent arrays may be NULL. Memory from
+ * b200p_host_alloc is pinned and takes the copies at link speed; any other host memory works,
+ * slower. If the block does not fit (cap_rows / cap_nnz), B200P_E_CAPACITY is returned, out->rows
+ * and out->nnz say what it needs, and the block stays queued for the next call.
+ */
+typedef struct b200p_destination {
+  uint64_t *offset;      /* cap_rows + 1 entries */
+  float *label;          /* cap_rows */
+  float *weight;         /* cap_rows (LibSVM, LibFM) */
+  uint64_t *qid;         /* cap_rows (LibSVM) */
+  void *field;           /* cap_nnz entries of index_bytes (LibFM) */
+  void *index;           /* cap_nnz entries of index_bytes */
+  float *value;          /* cap_nnz */
+  uint64_t cap_rows;
+  uint64_t cap_nnz;
+  uint64_t offset_base;
+} b200p_destination;
+int b200p_next_to(b200p_handle h, const b200p_destination *dst, b200p_rowblock *out);
+
+/* Pinned host memory on the handle's device, huge-page backed where the host allows it (what the
+   library uses for its own staging and result buffers). b200p_host_free works after the handle
+   is gone. No reference counterpart. */
+int b200p_host_alloc(b200p_handle h, uint64_t bytes, void **ptr);
+void b200p_host_free(void *ptr);
+
+/*
  * Host threads b200p_next may use (0..64). Their one job: for CSV chunks whose rows average 16
  * or more entries, index[] is not copied back from the GPU -- it is implied by offset[] (the j-th
  * non-label field of a row has column id j, src/data/csv_parser.h:84-88) -- but written into the

@@ -425,3 +425,68 @@ def test_libfm_field_ids_cross_the_link_as_bytes(cuda_lib, oracle, ib):
     saved = moved[0] - moved[4]
     # two small chunks save (ib - 1) bytes per entry minus the header; the large one costs its narrow copy
     assert saved == 2 * (nnz_small * (ib - 1) - 256) - (len(exp[1]["index"]) + 256)
+
+
+@pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA[:4])
+def test_next_to_lands_blocks_in_caller_memory(cuda_lib, oracle, kind, fmt, ib, lc):
+    """b200p_next_to: every block is written at the caller's running position in one set of
+    arrays (offsets rebased by offset_base), so the arrays end up being the whole parse -- what
+    BasicRowIter builds with RowBlockContainer::Push.  A block that does not fit stays queued."""
+    import ctypes
+    from dmlc_core_b200 import datagen
+    from dmlc_core_b200.capi import Destination
+    data, rows = datagen.generate(kind, 12, 5 << 20)
+    raw = data.tobytes()
+    exp = oracle.parse_buffer(fmt, raw, ib, lc)
+    cuts, pos = [0], 0
+    while pos < len(raw):
+        pos = min(len(raw), pos + (700 << 10))
+        if pos < len(raw):
+            pos = raw.index(b"\n", pos) + 1
+        cuts.append(pos)
+    nrows, nnz = len(exp["label"]), len(exp["index"])
+    p = _parser(cuda_lib, fmt, ib, lc, chunk_bytes=1 << 20, depth=3)
+    idt = np.uint64 if ib == 8 else np.uint32
+    sizes = {"offset": (nrows + 1) * 8, "label": nrows * 4, "weight": nrows * 4, "qid": nrows * 8,
+             "field": nnz * ib, "index": nnz * ib, "value": nnz * 4}
+    base = {k: p.host_alloc(max(v, 8)) for k, v in sizes.items()}
+    at_row = at_nnz = at_w = at_q = at_v = 0
+    refused = 0
+    chunks = [raw[a:b] for a, b in zip(cuts[:-1], cuts[1:])]
+    todo = list(chunks)
+    while todo or p.pending():
+        while todo and p.pending() < 3:
+            p.submit(todo.pop(0))
+        d = Destination()
+        d.offset, d.label = base["offset"] + 8 * at_row, base["label"] + 4 * at_row
+        d.weight, d.qid = base["weight"] + 4 * at_w, base["qid"] + 8 * at_q
+        d.field, d.index = base["field"] + ib * at_nnz, base["index"] + ib * at_nnz
+        d.value = base["value"] + 4 * at_v
+        d.offset_base = at_nnz
+        if refused == 0 and at_row != 0:           # once: offer too little room
+            d.cap_rows, d.cap_nnz = 1, 1
+            rc, blk = p.next_to(d)
+            assert rc == 6 and blk.rows > 1 and blk.nnz > 1
+            refused += 1
+        d.cap_rows, d.cap_nnz = nrows - at_row, nnz - at_nnz
+        rc, blk = p.next_to(d)
+        assert rc == 0
+        at_row += blk.rows
+        at_nnz += blk.nnz
+        at_w += blk.n_weight
+        at_q += blk.n_qid
+        at_v += blk.n_value
+    assert refused == 1 and (at_row, at_nnz) == (nrows, nnz)
+
+    def view(key, count, dtype):
+        buf = (ctypes.c_char * (count * np.dtype(dtype).itemsize)).from_address(base[key])
+        return np.frombuffer(buf, dtype=dtype).copy()
+
+    got = {"offset": view("offset", nrows + 1, np.uint64), "label": view("label", nrows, np.float32),
+           "weight": view("weight", at_w, np.float32), "qid": view("qid", at_q, np.uint64),
+           "field": view("field", nnz if fmt == "libfm" else 0, idt), "index": view("index", nnz, idt),
+           "value": view("value", at_v, np.float32), "error": 0}
+    for ptr in base.values():
+        p.host_free(ptr)
+    p.close()
+    assert same_rowblocks(got, exp) is None
