@@ -1128,14 +1128,34 @@ int b200p_next_to(b200p_handle h, const b200p_destination *dst, b200p_rowblock *
     s = &h->slots[id];
   }
   int rc = FinishParse(h, s);
+  Arrays to;
+  to.offset = reinterpret_cast<unsigned long long *>(dst->offset);
+  to.label = dst->label;
+  to.weight = dst->weight;
+  to.qid = reinterpret_cast<unsigned long long *>(dst->qid);
+  to.field = dst->field;
+  to.index = dst->index;
+  to.value = dst->value;
   std::memset(out, 0, sizeof(*out));
   if (rc == B200P_OK && s->nbytes != 0) {
+    /* refusals leave the block queued and say what it holds */
     const ChunkSummary &sum = *s->h_summary;
     out->rows = sum.total[kRows];
     out->nnz = sum.total[kNnz];
+    out->n_weight = sum.total[kWeights];
+    out->n_qid = sum.total[kQids];
+    out->n_value = sum.total[kValues];
+    out->n_field = h->cfg.format == B200P_FORMAT_LIBFM ? out->nnz : 0;
+    out->text_bytes = s->nbytes;
     if (sum.total[kRows] > dst->cap_rows || sum.total[kNnz] > dst->cap_nnz) {
       return Fail(h, B200P_E_CAPACITY, "b200p_next_to: the destination arrays are too small for the next block; "
-                                       "it stays queued (rows and nnz say how much room it needs)");
+                                       "it stays queued (the counts in *out say how much room it needs)");
+    }
+    if ((out->rows != 0 && (to.offset == NULL || to.label == NULL)) || (out->nnz != 0 && to.index == NULL) ||
+        (out->n_value != 0 && to.value == NULL) || (out->n_weight != 0 && to.weight == NULL) ||
+        (out->n_qid != 0 && to.qid == NULL) || (out->n_field != 0 && to.field == NULL)) {
+      return Fail(h, B200P_E_INVALID, "b200p_next_to: a destination array the next block needs is NULL; "
+                                      "it stays queued (the counts in *out say which)");
     }
   }
   {
@@ -1146,22 +1166,7 @@ int b200p_next_to(b200p_handle h, const b200p_destination *dst, b200p_rowblock *
     h->last_block = NULL;
   }
   if (rc != B200P_OK) return rc;
-  Arrays to;
-  to.offset = reinterpret_cast<unsigned long long *>(dst->offset);
-  to.label = dst->label;
-  to.weight = dst->weight;
-  to.qid = reinterpret_cast<unsigned long long *>(dst->qid);
-  to.field = dst->field;
-  to.index = dst->index;
-  to.value = dst->value;
   if (s->nbytes != 0) {
-    const ChunkSummary &sum = *s->h_summary;
-    if ((sum.total[kRows] != 0 && (to.offset == NULL || to.label == NULL)) ||
-        (sum.total[kNnz] != 0 && to.index == NULL) || (sum.total[kValues] != 0 && to.value == NULL) ||
-        (sum.total[kWeights] != 0 && to.weight == NULL) || (sum.total[kQids] != 0 && to.qid == NULL) ||
-        (h->cfg.format == B200P_FORMAT_LIBFM && sum.total[kNnz] != 0 && to.field == NULL)) {
-      return Fail(h, B200P_E_INVALID, "b200p_next_to: a destination array this block needs is NULL");
-    }
     rc = DeliverBlock(h, s, to, dst->offset_base);
     if (rc != B200P_OK) return rc;
   }

@@ -23,6 +23,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <exception>
+#include <functional>
 #include <limits>
 #include <mutex>
 #include <thread>
@@ -175,6 +176,36 @@ class B200TextParser : public Parser<IndexType> {
     uint64_t mi = 0, mf = 0;
     BlockMax(&mi, &mf);
     return mi;
+  }
+  /* Next() with the block written straight behind what the caller already holds
+     (b200p_next_to).  kRefused: the next block does not fit `dst` or needs an array `dst` lacks;
+     it stays queued, *blk says what it holds, and Next() can still fetch it the ordinary way. */
+  enum IntoResult { kIntoEnd, kIntoDone, kIntoRefused };
+  IntoResult NextInto(const b200p_destination &dst, b200p_rowblock *blk) {
+    for (;;) {
+      if (text_ != NULL) {
+        if (!WaitForFeeder()) return kIntoEnd;
+      } else {
+        Feed();
+        if (b200p_pending(handle_) == 0) return kIntoEnd;
+      }
+      const int rc = b200p_next_to(handle_, &dst, blk);
+      if ((rc == B200P_E_CAPACITY || rc == B200P_E_INVALID) && blk->text_bytes != 0) return kIntoRefused;
+      if (text_ != NULL) {   /* a pipeline slot came free */
+        { std::lock_guard<std::mutex> g(feeder_mu_); }
+        feeder_cv_.notify_all();
+      }
+      Check(rc);
+      bytes_read_ += blk->text_bytes;
+      if (blk->rows == 0) continue;
+      return kIntoDone;
+    }
+  }
+  /* pinned host memory that takes device-to-host copies at link speed (b200p_host_alloc) */
+  void *HostAlloc(size_t bytes) {
+    void *p = NULL;
+    Check(b200p_host_alloc(handle_, bytes, &p));
+    return p;
   }
   /* text bytes of this parser's partition when the source can tell (files), else 0 */
   size_t PartitionBytes() const {
@@ -404,8 +435,13 @@ Parser<IndexType> *CreateParserImpl(const char *uri, unsigned part_index, unsign
 template <typename T>
 class HugeArray {
  public:
-  HugeArray() : p_(NULL), n_(0), cap_(0) {}
-  ~HugeArray() { std::free(p_); }
+  HugeArray() : p_(NULL), n_(0), cap_(0), pinned_(false) {}
+  ~HugeArray() { Release(); }
+  /* from now on memory comes from `alloc` (pinned by the GPU library, freed with b200p_host_free) */
+  void UsePinned(const std::function<void *(size_t)> &alloc) { alloc_ = alloc; }
+  T *End() { return p_ + n_; }
+  size_t Room() const { return cap_ - n_; }
+  void Commit(size_t k) { n_ += k; }
   size_t size() const { return n_; }
   bool empty() const { return n_ == 0; }
   const T *data() const { return n_ != 0 ? p_ : NULL; }   /* NULL when empty, like BeginPtr */
@@ -415,12 +451,17 @@ class HugeArray {
     const size_t kAlign = 2u << 20;
     const size_t bytes = (cap * sizeof(T) + kAlign - 1) / kAlign * kAlign;
     void *q = NULL;
-    CHECK(posix_memalign(&q, kAlign, bytes) == 0) << "out of memory growing a RowBlock array";
+    if (alloc_) {
+      q = alloc_(bytes);
+    } else {
+      CHECK(posix_memalign(&q, kAlign, bytes) == 0) << "out of memory growing a RowBlock array";
 #ifdef MADV_HUGEPAGE
-    madvise(q, bytes, MADV_HUGEPAGE);
+      madvise(q, bytes, MADV_HUGEPAGE);
 #endif
+    }
     if (n_ != 0) std::memcpy(q, p_, n_ * sizeof(T));
-    std::free(p_);
+    Release();
+    pinned_ = static_cast<bool>(alloc_);
     p_ = static_cast<T *>(q);
     cap_ = bytes / sizeof(T);
   }
@@ -434,8 +475,14 @@ class HugeArray {
   void push_back(const T &v) { *Extend(1) = v; }
 
  private:
+  void Release() {
+    if (pinned_) b200p_host_free(p_); else std::free(p_);
+    p_ = NULL;
+  }
   T *p_;
   size_t n_, cap_;
+  bool pinned_;
+  std::function<void *(size_t)> alloc_;
   HugeArray(const HugeArray &);
   void operator=(const HugeArray &);
 };
@@ -461,12 +508,42 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
     try {
       bool first = true;
       double t_next = 0, t_append = 0, t_max = 0;   /* DMLC_B200_ITER_TRACE: where the load went */
+      const bool direct = gpu != NULL && std::getenv("DMLC_B200_ITER_COPY") == NULL;
       for (;;) {
         double ta = GetTime();
+        if (direct && !first) {
+          /* every block after the first lands behind what is already here, no block in between */
+          b200p_destination dst;
+          b200p_rowblock blk;
+          AimAtEnds(&dst);
+          const typename B200TextParser<IndexType>::IntoResult got = gpu->NextInto(dst, &blk);
+          if (got == B200TextParser<IndexType>::kIntoEnd) break;
+          if (got == B200TextParser<IndexType>::kIntoDone) {
+            t_next += GetTime() - ta;
+            ta = GetTime();
+            CommitBlock(blk);
+            max_index_ = std::max(max_index_, static_cast<IndexType>(gpu->BlockMaxIndex()));
+            t_max += GetTime() - ta;
+            continue;
+          }
+          if (MakeRoomFor(blk)) continue;   /* grown: ask again */
+          /* the block needs an array this load never had (weights or qids appearing late):
+             take it the ordinary way */
+        }
         if (!parser->Next()) break;
         t_next += GetTime() - ta;
         ta = GetTime();
         const RowBlock<IndexType> &b = parser->Value();
+        if (first && direct) {
+          const std::function<void *(size_t)> pinned = [gpu](size_t bytes) { return gpu->HostAlloc(bytes); };
+          offset_.UsePinned(pinned);
+          label_.UsePinned(pinned);
+          weight_.UsePinned(pinned);
+          qid_.UsePinned(pinned);
+          field_.UsePinned(pinned);
+          index_.UsePinned(pinned);
+          value_.UsePinned(pinned);
+        }
         if (first && total_bytes != 0 && parser->BytesRead() != 0) {
           /* size everything once: this block's rows and entries per text byte, plus 5 % */
           const double scale = 1.05 * static_cast<double>(total_bytes) / parser->BytesRead();
@@ -530,6 +607,57 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
     const void *src;
     size_t bytes;
   };
+  /* destination of the next block: the ends of the arrays, and how much room they have */
+  void AimAtEnds(b200p_destination *dst) {
+    std::memset(dst, 0, sizeof(*dst));
+    dst->offset = reinterpret_cast<uint64_t *>(offset_.End() - 1);   /* rewrites the last entry in place */
+    dst->label = label_.End();
+    dst->weight = weight_.Room() != 0 ? weight_.End() : NULL;
+    dst->qid = qid_.Room() != 0 ? qid_.End() : NULL;
+    dst->field = field_.Room() != 0 ? field_.End() : NULL;
+    dst->index = index_.End();
+    dst->value = value_.Room() != 0 ? value_.End() : NULL;
+    size_t rows = std::min(offset_.Room(), label_.Room());
+    if (!weight_.empty()) rows = std::min(rows, weight_.Room());
+    if (!qid_.empty()) rows = std::min(rows, qid_.Room());
+    size_t nnz = index_.Room();
+    if (!field_.empty()) nnz = std::min(nnz, field_.Room());
+    if (!value_.empty()) nnz = std::min(nnz, value_.Room());
+    dst->cap_rows = rows;
+    dst->cap_nnz = nnz;
+    dst->offset_base = offset_.back();
+  }
+  /* the block NextInto wrote is now part of the arrays (same lengths Append would add) */
+  void CommitBlock(const b200p_rowblock &blk) {
+    offset_.Commit(blk.rows);
+    label_.Commit(blk.rows);
+    if (blk.weight != NULL) weight_.Commit(blk.rows);
+    if (blk.qid != NULL) qid_.Commit(blk.rows);
+    if (blk.field != NULL) field_.Commit(blk.nnz);
+    index_.Commit(blk.nnz);
+    if (blk.value != NULL) value_.Commit(blk.nnz);
+  }
+  /* after a refusal: grow what the block needs; false when it needs an array that has never
+     been used in this load (then the ordinary path appends it) */
+  bool MakeRoomFor(const b200p_rowblock &blk) {
+    if ((blk.n_weight != 0 && weight_.empty()) || (blk.n_qid != 0 && qid_.empty()) ||
+        (blk.n_field != 0 && field_.empty()) || (blk.n_value != 0 && value_.empty())) {
+      return false;
+    }
+    const size_t rows = static_cast<size_t>(blk.rows), nnz = static_cast<size_t>(blk.nnz);
+    Grow(&offset_, rows);
+    Grow(&label_, rows);
+    if (!weight_.empty()) Grow(&weight_, rows);
+    if (!qid_.empty()) Grow(&qid_, rows);
+    if (!field_.empty()) Grow(&field_, nnz);
+    Grow(&index_, nnz);
+    if (!value_.empty()) Grow(&value_, nnz);
+    return true;
+  }
+  template <typename T>
+  static void Grow(HugeArray<T> *a, size_t more) {
+    if (a->Room() < more) a->Reserve(a->size() + std::max(more, a->size() / 2));
+  }
   template <typename T>
   void Plan(HugeArray<T> *to, const T *from, size_t count, std::vector<Piece> *plan) {
     if (from == NULL || count == 0) return;
