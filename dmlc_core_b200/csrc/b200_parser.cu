@@ -1162,7 +1162,9 @@ int b200p_next_to(b200p_handle h, const b200p_destination *dst, b200p_rowblock *
     std::lock_guard<std::mutex> g(h->mu);
     h->in_flight.pop_front();
     s->busy = false;
-    h->returned_slot = -1;     /* nothing of any slot is lent out: the arrays are the caller's */
+    /* the slot stays held, as after b200p_next: its device arrays feed the copies below and
+       b200p_block_max until the next block is taken */
+    h->returned_slot = id;
     h->last_block = NULL;
   }
   if (rc != B200P_OK) return rc;

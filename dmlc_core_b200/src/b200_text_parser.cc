@@ -202,10 +202,9 @@ class B200TextParser : public Parser<IndexType> {
     }
   }
   /* pinned host memory that takes device-to-host copies at link speed (b200p_host_alloc) */
-  void *HostAlloc(size_t bytes) {
+  void *HostAlloc(size_t bytes) {   /* NULL when the host will not pin that much */
     void *p = NULL;
-    Check(b200p_host_alloc(handle_, bytes, &p));
-    return p;
+    return b200p_host_alloc(handle_, bytes, &p) == B200P_OK ? p : NULL;
   }
   /* text bytes of this parser's partition when the source can tell (files), else 0 */
   size_t PartitionBytes() const {
@@ -451,9 +450,12 @@ class HugeArray {
     const size_t kAlign = 2u << 20;
     const size_t bytes = (cap * sizeof(T) + kAlign - 1) / kAlign * kAlign;
     void *q = NULL;
+    bool pinned = false;
     if (alloc_) {
       q = alloc_(bytes);
-    } else {
+      pinned = q != NULL;   /* a host that refuses to pin this much still gets ordinary memory */
+    }
+    if (q == NULL) {
       CHECK(posix_memalign(&q, kAlign, bytes) == 0) << "out of memory growing a RowBlock array";
 #ifdef MADV_HUGEPAGE
       madvise(q, bytes, MADV_HUGEPAGE);
@@ -461,7 +463,7 @@ class HugeArray {
     }
     if (n_ != 0) std::memcpy(q, p_, n_ * sizeof(T));
     Release();
-    pinned_ = static_cast<bool>(alloc_);
+    pinned_ = pinned;
     p_ = static_cast<T *>(q);
     cap_ = bytes / sizeof(T);
   }
@@ -535,7 +537,11 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
         ta = GetTime();
         const RowBlock<IndexType> &b = parser->Value();
         if (first && direct) {
-          const std::function<void *(size_t)> pinned = [gpu](size_t bytes) { return gpu->HostAlloc(bytes); };
+          /* DMLC_B200_ITER_NO_PIN: behave like a host that refuses to pin (ordinary memory) */
+          const bool may_pin = std::getenv("DMLC_B200_ITER_NO_PIN") == NULL;
+          const std::function<void *(size_t)> pinned = [gpu, may_pin](size_t bytes) {
+            return may_pin ? gpu->HostAlloc(bytes) : static_cast<void *>(NULL);
+          };
           offset_.UsePinned(pinned);
           label_.UsePinned(pinned);
           weight_.UsePinned(pinned);

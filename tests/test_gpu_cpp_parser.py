@@ -289,3 +289,23 @@ def test_parser_on_stdin(hostapi, oracle, tmp_path):
     got = {k: z[k] for k in ("offset", "label", "weight", "qid", "field", "index", "value")}
     got["error"] = 0
     assert same_rowblocks(got, exp) is None and int(z["nblocks"]) >= 6
+
+
+@pytest.mark.parametrize("mode", ["in place", "in place, not pinned", "copying"])
+def test_row_block_iter_modes_agree(hostapi, oracle, tmp_path, monkeypatch, mode):
+    """RowBlockIter::Create lets blocks land in its own (pinned) arrays; on a host that refuses to
+    pin, and with the copying path forced, the result is the same."""
+    from dmlc_core_b200 import datagen
+    monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
+    if mode == "in place, not pinned":
+        monkeypatch.setenv("DMLC_B200_ITER_NO_PIN", "1")
+    if mode == "copying":
+        monkeypatch.setenv("DMLC_B200_ITER_COPY", "1")
+    for kind, fmt, ib in (("libsvm_qid", "libsvm", 4), ("libfm", "libfm", 8), ("csv", "csv", 4)):
+        data, rows = datagen.generate(kind, 19, 7 << 20)
+        f = tmp_path / (kind + ".txt")
+        f.write_bytes(data.tobytes())
+        exp = oracle.parse_buffer(fmt, data.tobytes(), ib, -1)
+        got, ncol, _ = hostapi.row_iter(str(f), 0, 1, fmt, ib)
+        assert same_rowblocks(_trim_hidden_lengths(got, exp), exp) is None, (mode, kind)
+        assert ncol == int(exp["index"].max()) + 1
