@@ -27,6 +27,7 @@
 #include "../../include/dmlc_b200_parser.h"
 #include "host_pool.h"
 #include "text_kernels.cuh"
+#include "tile_kernels.cuh"
 
 namespace b200p {
 
@@ -63,6 +64,9 @@ struct Slot {
   uint64_t text_cap;
   uint32_t *d_counts;
   uint64_t counts_cap; /* in ranges */
+  unsigned char *d_tiles; /* one-launch kernel: ticket + look-back status words */
+  uint64_t tiles_cap;     /* in tiles */
+  bool ran_tiles;         /* the chunk in flight went through ParseTiles */
   ChunkSummary *d_summary;
   ChunkSummary *h_summary; /* pinned */
   Arrays dev;
@@ -116,6 +120,12 @@ struct b200p_parser_s {
   std::mutex mu, err_mu, prof_mu;
   unsigned long long *d_max; /* two words for b200p_block_max, allocated on first use */
   std::atomic<bool> saw_qids; /* a LibSVM chunk reported qids: later launches use the QID kernels */
+  /* one-launch kernel (ParseTiles): used while the input suits it; a chunk it gives up on is
+     parsed again by the two-pass kernels, and after kTileStrikes such chunks the handle stays
+     with the two-pass kernels */
+  std::atomic<bool> use_tiles;
+  std::atomic<int> tile_fallbacks;
+  uint32_t sub_bytes, over_bytes, pool_div;
   int host_threads;          /* b200p_set_host_threads; 0 = column ids always come from the GPU */
   HostPool *pool;            /* created on first use */
   std::vector<uint64_t> iota; /* 0, 1, 2, ... in the handle's index width */
@@ -463,6 +473,86 @@ static WalkParams MakeParams(const b200p_handle h, const Slot &s) {
   return p;
 }
 
+
+/* ---- the one-launch kernel (tile_kernels.cuh) ---- */
+static const int kTileStrikes = 2;
+
+static bool TilesSuit(const b200p_handle h) {
+  /* CSV with the label in a later column needs a column id per field: two-pass kernels */
+  return h->use_tiles && !(h->cfg.format == B200P_FORMAT_CSV && h->cfg.label_column > 0);
+}
+
+static TileParams MakeTileParams(const b200p_handle h, const Slot &s) {
+  TileParams p;
+  std::memset(&p, 0, sizeof(p));
+  p.text = s.text;
+  p.size = static_cast<uint32_t>(s.nbytes);
+  p.sub_bytes = h->sub_bytes;
+  p.over_bytes = h->cfg.format == B200P_FORMAT_CSV ? static_cast<uint32_t>(kStepBytes) : h->over_bytes;
+  const uint64_t tile_bytes = static_cast<uint64_t>(kTileWarps) * p.sub_bytes;
+  p.num_tiles = static_cast<uint32_t>((s.nbytes + tile_bytes - 1) / tile_bytes);
+  p.label_column = h->cfg.label_column;
+  p.four = 4u;
+  p.sixteen = 16u;
+  /* queue capacities per warp.  CSV: a sub-range cannot start more than sub_bytes / 2 fields.
+     LibSVM / LibFM: the lines a warp owns may run into the overhang; text denser than about one
+     token per four bytes sends the chunk to the two-pass kernels. */
+  p.cap_pool = h->cfg.format == B200P_FORMAT_CSV ? p.sub_bytes / 2u : std::max(256u, p.sub_bytes / h->pool_div);
+  p.cap_rows = h->cfg.format == B200P_FORMAT_CSV ? std::max(64u, p.sub_bytes / 8u) : std::max(64u, p.sub_bytes / 16u);
+  p.scratch = s.d_tiles;
+  p.summary = s.d_summary;
+  p.offset = s.dev.offset;
+  p.label = s.dev.label;
+  p.weight = s.dev.weight;
+  p.qid = s.dev.qid;
+  p.field = s.dev.field;
+  p.index = s.dev.index;
+  p.value = s.dev.value;
+  p.out_rows = s.dev.cap_rows;
+  p.out_nnz = s.dev.cap_nnz;
+  return p;
+}
+
+static uint64_t TileScratchBytes(uint64_t tiles) {
+  return kTileHeaderBytes + tiles * 2ull * kStatusWords * sizeof(unsigned long long);
+}
+
+template <int FMT, typename IdxT, bool QID>
+static cudaError_t LaunchTilesAs(const TileParams &p, cudaStream_t st) {
+  const uint32_t smem = TileSmemBytes<FMT>(p);
+  const cudaError_t e = cudaFuncSetAttribute(ParseTiles<FMT, IdxT, QID>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  if (e != cudaSuccess) return e;
+  ParseTiles<FMT, IdxT, QID><<<p.num_tiles, kTileThreads, smem, st>>>(p);
+  return cudaGetLastError();
+}
+
+static cudaError_t LaunchTiles(int format, bool wide, bool qids, const TileParams &p, cudaStream_t st) {
+  if (format == B200P_FORMAT_LIBSVM) {
+    if (qids) return wide ? LaunchTilesAs<kLibSVM, uint64_t, true>(p, st) : LaunchTilesAs<kLibSVM, uint32_t, true>(p, st);
+    return wide ? LaunchTilesAs<kLibSVM, uint64_t, false>(p, st) : LaunchTilesAs<kLibSVM, uint32_t, false>(p, st);
+  }
+  if (format == B200P_FORMAT_LIBFM) {
+    return wide ? LaunchTilesAs<kLibFM, uint64_t, false>(p, st) : LaunchTilesAs<kLibFM, uint32_t, false>(p, st);
+  }
+  return wide ? LaunchTilesAs<kCSV, uint64_t, false>(p, st) : LaunchTilesAs<kCSV, uint32_t, false>(p, st);
+}
+
+/* clear the look-back scratch and the summary, one launch, summary to the host */
+static int EnqueueTiles(b200p_handle h, Slot *s) {
+  const TileParams p = MakeTileParams(h, *s);
+  CUDA_TRY(h, cudaMemsetAsync(s->d_tiles, 0, TileScratchBytes(p.num_tiles), s->stream));
+  CUDA_TRY(h, cudaMemsetAsync(s->d_summary, 0, sizeof(ChunkSummary), s->stream));
+  ProfBegin(h, B200P_KERNEL_EMIT, s->stream);
+  const cudaError_t e = LaunchTiles(h->cfg.format, h->cfg.index_bytes == 8, h->saw_qids, p, s->stream);
+  ProfEnd(h, s->stream);
+  ++h->launches;
+  CUDA_TRY(h, e);
+  CUDA_TRY(h, cudaMemcpyAsync(s->h_summary, s->d_summary, sizeof(ChunkSummary),
+                              cudaMemcpyDeviceToHost, s->stream));
+  return B200P_OK;
+}
+
 /* pass 2 (+ the CSV label clear), then the summary travels to the host */
 static int EnqueueEmit(b200p_handle h, Slot *s) {
   const WalkParams p = MakeParams(h, *s);
@@ -480,12 +570,21 @@ static int EnqueueEmit(b200p_handle h, Slot *s) {
   return B200P_OK;
 }
 
-/* pass 1 + scan + (speculative) pass 2 for the chunk described by s->text / s->nbytes */
-static int EnqueueParse(b200p_handle h, Slot *s) {
-  if (s->nbytes == 0) {
-    std::memset(s->h_summary, 0, sizeof(ChunkSummary));
-    return B200P_OK;
+/* output arrays for a chunk whose counts are not known yet */
+static int ProvisionArrays(b200p_handle h, Slot *s) {
+  uint64_t want_rows, want_nnz;
+  Provision(h, s->nbytes, &want_rows, &want_nnz);
+  if (want_rows > s->dev.cap_rows || want_nnz > s->dev.cap_nnz || s->dev.offset == NULL) {
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+    const int rc = EnsureArrays(h, &s->dev, want_rows, want_nnz, false);
+    if (rc != B200P_OK) return rc;
   }
+  return B200P_OK;
+}
+
+/* pass 1 + scan + (speculative) pass 2 for the chunk described by s->text / s->nbytes */
+static int EnqueueTwoPass(b200p_handle h, Slot *s) {
+  s->ran_tiles = false;
   const uint32_t range_bytes = RangeBytesFor(h, s->nbytes);
   const uint64_t ranges = (s->nbytes + range_bytes - 1) / range_bytes;
   if (ranges > s->counts_cap) {
@@ -499,13 +598,8 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
                            (cap + cap / kScanTile + 2) * kNumCounters * sizeof(uint32_t)));
     s->counts_cap = cap;
   }
-  uint64_t want_rows, want_nnz;
-  Provision(h, s->nbytes, &want_rows, &want_nnz);
-  if (want_rows > s->dev.cap_rows || want_nnz > s->dev.cap_nnz || s->dev.offset == NULL) {
-    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
-    const int rc = EnsureArrays(h, &s->dev, want_rows, want_nnz, false);
-    if (rc != B200P_OK) return rc;
-  }
+  const int rc = ProvisionArrays(h, s);
+  if (rc != B200P_OK) return rc;
   const WalkParams p = MakeParams(h, *s);
   ProfBegin(h, B200P_KERNEL_COUNT, s->stream);
   LaunchWalk(h, p, s->stream, false);
@@ -519,16 +613,50 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
   return EnqueueEmit(h, s);
 }
 
+/* the kernels for the chunk described by s->text / s->nbytes: one launch where the input suits
+   ParseTiles, the two-pass walk otherwise */
+static int EnqueueParse(b200p_handle h, Slot *s) {
+  if (s->nbytes == 0) {
+    std::memset(s->h_summary, 0, sizeof(ChunkSummary));
+    return B200P_OK;
+  }
+  if (!TilesSuit(h)) return EnqueueTwoPass(h, s);
+  const uint64_t tile_bytes = static_cast<uint64_t>(kTileWarps) * h->sub_bytes;
+  const uint64_t tiles = (s->nbytes + tile_bytes - 1) / tile_bytes;
+  if (tiles > s->tiles_cap) {
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+    cudaFree(s->d_tiles);
+    s->d_tiles = NULL;
+    s->tiles_cap = 0;
+    const uint64_t cap = tiles + tiles / 4 + 16;
+    CUDA_TRY(h, DeviceAlloc(reinterpret_cast<void **>(&s->d_tiles), TileScratchBytes(cap)));
+    s->tiles_cap = cap;
+  }
+  const int rc = ProvisionArrays(h, s);
+  if (rc != B200P_OK) return rc;
+  s->ran_tiles = true;
+  return EnqueueTiles(h, s);
+}
+
 /* Wait for the chunk, re-run pass 2 with larger arrays if the provision was too small, and
    translate device error bits. On success the device arrays of `s` hold the chunk. */
 static int FinishParse(b200p_handle h, Slot *s) {
   if (s->nbytes == 0) return B200P_OK;
   CUDA_TRY(h, cudaStreamSynchronize(s->stream));
   const ChunkSummary &sum = *s->h_summary;
+  if (s->ran_tiles && (sum.error & kErrFallback) != 0u && (sum.error & kErrInternal) == 0u) {
+    /* the one-launch kernel met something it does not take (a line longer than its overhang,
+       text denser than its queues): this chunk goes through the two-pass kernels, and a handle
+       that keeps meeting such chunks stops trying */
+    if (++h->tile_fallbacks >= kTileStrikes) h->use_tiles = false;
+    const int rc = EnqueueTwoPass(h, s);
+    if (rc != B200P_OK) return rc;
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+  }
   if (sum.total[kRows] > s->dev.cap_rows || sum.total[kNnz] > s->dev.cap_nnz) {
     const int rc = EnsureArrays(h, &s->dev, sum.total[kRows], sum.total[kNnz], false);
     if (rc != B200P_OK) return rc;
-    const int rc2 = EnqueueEmit(h, s);
+    const int rc2 = s->ran_tiles ? EnqueueTiles(h, s) : EnqueueEmit(h, s);
     if (rc2 != B200P_OK) return rc2;
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
   }
@@ -581,6 +709,7 @@ static void DestroySlot(Slot *s) {
   PinnedFree(s->h_narrow);
   cudaFree(s->d_text);
   cudaFree(s->d_counts);
+  cudaFree(s->d_tiles);
   cudaFree(s->d_summary);
   cudaFreeHost(s->h_summary);
   FreeDeviceArrays(&s->dev);
@@ -696,6 +825,24 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->launches = 0;
   h->d_max = NULL;
   h->saw_qids = false;
+  {
+    /* B200P_TILES=0 keeps a process on the two-pass kernels (comparisons, tests of that path);
+       B200P_SUB_BYTES / B200P_OVER_BYTES are tuning knobs of the one-launch kernel */
+    const char *off = std::getenv("B200P_TILES");
+    h->use_tiles = !(off != NULL && off[0] == '0');
+    h->tile_fallbacks = 0;
+    uint32_t sub = 2048u, over = 4096u;
+    const char *e1 = std::getenv("B200P_SUB_BYTES"), *e2 = std::getenv("B200P_OVER_BYTES");
+    if (e1 != NULL && std::atoi(e1) > 0) sub = static_cast<uint32_t>(std::atoi(e1));
+    if (e2 != NULL && std::atoi(e2) > 0) over = static_cast<uint32_t>(std::atoi(e2));
+    if (rb != 0u) sub = rb;     /* config.range_bytes: bytes of text one warp owns, in both kernels */
+    sub = std::min<uint32_t>(4096u, std::max<uint32_t>(kStepBytes, sub / kStepBytes * kStepBytes));
+    over = std::min<uint32_t>(16384u, std::max<uint32_t>(kStepBytes, (over + kStepBytes - 1) / kStepBytes * kStepBytes));
+    h->sub_bytes = sub;
+    h->over_bytes = over;
+    const char *e3 = std::getenv("B200P_POOL_DIV");
+    h->pool_div = (e3 != NULL && std::atoi(e3) >= 2 && std::atoi(e3) <= 16) ? static_cast<uint32_t>(std::atoi(e3)) : 4u;
+  }
   h->pool = NULL;
   h->copied_h2d = h->copied_d2h = 0;
   {

@@ -31,8 +31,56 @@
 
 namespace b200p {
 
+#if defined(__CUDA_ARCH__)
+B200P_D uint32_t Load4(const uint8_t *p) { return __ldg(reinterpret_cast<const uint32_t *>(p)); }
+/* x << s for s = 0..32 (32 gives 0) */
+B200P_D uint32_t ShlClamp(uint32_t x, uint32_t s) { return __funnelshift_lc(0u, x, s); }
+/* bytes k.. of the 8-byte pair (hi:lo), k = 0..3 */
+B200P_D uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) { return __funnelshift_r(lo, hi, k * 8u); }
+B200P_D int FirstSet(uint32_t x) { return __ffs(static_cast<int>(x)) - 1; }
+B200P_D float U32ToFloat(uint32_t x) { return __uint2float_rn(x); }
+B200P_D float Fraction8(uint32_t f8) {
+  return __double2float_rn(__dmul_rn(__uint2double_rn(f8), 1e-8));
+}
+B200P_D float Fraction9(uint32_t f9) {
+  return __double2float_rn(__dmul_rn(__uint2double_rn(f9), 1e-9));
+}
+#else
+inline uint32_t Load4(const uint8_t *p) {
+  uint32_t a = 0;
+  for (int i = 0; i < 4; ++i) a |= static_cast<uint32_t>(p[i]) << (8 * i);
+  return a;
+}
+inline uint32_t ShlClamp(uint32_t x, uint32_t s) { return s >= 32u ? 0u : (x << s); }
+inline uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) {
+  return k == 0u ? lo : ((lo >> (8u * k)) | (hi << (32u - 8u * k)));
+}
+inline int FirstSet(uint32_t x) { return __builtin_ffs(static_cast<int>(x)) - 1; }
+inline float U32ToFloat(uint32_t x) { return static_cast<float>(x); }
+inline float Fraction8(uint32_t f8) {
+  volatile double q = static_cast<double>(f8) * 1e-8;
+  return static_cast<float>(q);
+}
+inline float Fraction9(uint32_t f9) {
+  volatile double q = static_cast<double>(f9) * 1e-9;
+  return static_cast<float>(q);
+}
+#endif
+
+
+/* 16 bytes of text starting at some position, as four little-endian words */
+struct Window {
+  uint32_t x0, x1, x2, x3;
+};
+
 /* A chunk of text in HBM. Reads at or beyond `size` yield NUL, which is what the reference
-   sees past a chunk (it zero-pads, reference src/io/input_split_base.cc:247). */
+   sees past a chunk (it zero-pads, reference src/io/input_split_base.cc:247).
+   The converters below are templates over the text source; a source offers
+     at(i)          one byte (NUL past the end)
+     Window16(p,w)  the 16 bytes at p as four words, false when they cannot be had cheaply
+     Tail8(p,a,b)   bytes 16..23 after p as two words, same convention
+   Text is the plain one (global memory); the fused kernel adds a source that serves windows
+   from the tile staged in shared memory (tile_kernels.cuh). */
 struct Text {
   const uint8_t *data;
   uint32_t size;
@@ -42,6 +90,28 @@ struct Text {
 #else
     return i < size ? static_cast<uint32_t>(data[i]) : 0u;
 #endif
+  }
+  /* false if the aligned loads would touch memory past the chunk
+     ([p & ~3, (p & ~3) + 20) must be readable) */
+  B200P_HD bool Window16(uint32_t p, Window *w) const {
+    const uint32_t a = p & ~3u;
+    if (a + 20u > size) return false;
+    const uint32_t w0 = Load4(data + a), w1 = Load4(data + a + 4), w2 = Load4(data + a + 8),
+                   w3 = Load4(data + a + 12), w4 = Load4(data + a + 16);
+    const uint32_t k = p & 3u;
+    w->x0 = BytesFrom(w0, w1, k);
+    w->x1 = BytesFrom(w1, w2, k);
+    w->x2 = BytesFrom(w2, w3, k);
+    w->x3 = BytesFrom(w3, w4, k);
+    return true;
+  }
+  B200P_HD bool Tail8(uint32_t p, uint32_t *x4, uint32_t *x5) const {
+    const uint32_t a = p & ~3u, k = p & 3u;
+    if (a + 28u > size) return false;
+    const uint32_t w4 = Load4(data + a + 16), w5 = Load4(data + a + 20), w6 = Load4(data + a + 24);
+    *x4 = BytesFrom(w4, w5, k);
+    *x5 = BytesFrom(w5, w6, k);
+    return true;
   }
 };
 
@@ -119,7 +189,8 @@ B200P_HD float ScaleOfTen(uint32_t e) {
  *   [space]* [+-]? digit* ( '.' digit* )? ( [eE] [+-]? digit* )?
  * `end` (optional) receives the position of the first byte not consumed.
  */
-B200P_HD float ToFloat(const Text &t, uint32_t p, uint32_t *end) {
+template <typename TXT>
+B200P_HD float ToFloat(const TXT &t, uint32_t p, uint32_t *end) {
   uint32_t c = t.at(p);
   while (IsSpace(c)) c = t.at(++p);
   bool negative = false;
@@ -182,8 +253,8 @@ B200P_HD float ToFloat(const Text &t, uint32_t p, uint32_t *end) {
  * 32-bit int => result mod 2^32, strtonum.h:186-190); WIDE=true mirrors Str2T<uint64_t>.
  * A '-' sign makes the reference CHECK fail (:141): reported through *negative.
  */
-template <bool WIDE>
-B200P_HD uint64_t ToUint(const Text &t, uint32_t p, bool *negative) {
+template <bool WIDE, typename TXT>
+B200P_HD uint64_t ToUint(const TXT &t, uint32_t p, bool *negative) {
   uint32_t c = t.at(p);
   while (IsSpace(c)) c = t.at(++p);
   if (c == '-') {
@@ -209,7 +280,8 @@ B200P_HD uint64_t ToUint(const Text &t, uint32_t p, bool *negative) {
 }
 
 /* qid: glibc atoll -- C-locale whitespace (' ' and \t..\r), sign, digits, saturating. */
-B200P_HD uint64_t ToQid(const Text &t, uint32_t p) {
+template <typename TXT>
+B200P_HD uint64_t ToQid(const TXT &t, uint32_t p) {
   uint32_t c = t.at(p);
   while (c == ' ' || (c - 9u) < 5u) c = t.at(++p);
   bool negative = false;
@@ -253,62 +325,6 @@ B200P_HD uint64_t ToQid(const Text &t, uint32_t p) {
  * exhaustively on the CPU (all 1 111 111 111 cases), so one DMUL replaces the
  * IEEE fp64 division.
  * ------------------------------------------------------------------------------------------ */
-#if defined(__CUDA_ARCH__)
-B200P_D uint32_t Load4(const uint8_t *p) { return __ldg(reinterpret_cast<const uint32_t *>(p)); }
-/* x << s for s = 0..32 (32 gives 0) */
-B200P_D uint32_t ShlClamp(uint32_t x, uint32_t s) { return __funnelshift_lc(0u, x, s); }
-/* bytes k.. of the 8-byte pair (hi:lo), k = 0..3 */
-B200P_D uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) { return __funnelshift_r(lo, hi, k * 8u); }
-B200P_D int FirstSet(uint32_t x) { return __ffs(static_cast<int>(x)) - 1; }
-B200P_D float U32ToFloat(uint32_t x) { return __uint2float_rn(x); }
-B200P_D float Fraction8(uint32_t f8) {
-  return __double2float_rn(__dmul_rn(__uint2double_rn(f8), 1e-8));
-}
-B200P_D float Fraction9(uint32_t f9) {
-  return __double2float_rn(__dmul_rn(__uint2double_rn(f9), 1e-9));
-}
-#else
-inline uint32_t Load4(const uint8_t *p) {
-  uint32_t a = 0;
-  for (int i = 0; i < 4; ++i) a |= static_cast<uint32_t>(p[i]) << (8 * i);
-  return a;
-}
-inline uint32_t ShlClamp(uint32_t x, uint32_t s) { return s >= 32u ? 0u : (x << s); }
-inline uint32_t BytesFrom(uint32_t lo, uint32_t hi, uint32_t k) {
-  return k == 0u ? lo : ((lo >> (8u * k)) | (hi << (32u - 8u * k)));
-}
-inline int FirstSet(uint32_t x) { return __builtin_ffs(static_cast<int>(x)) - 1; }
-inline float U32ToFloat(uint32_t x) { return static_cast<float>(x); }
-inline float Fraction8(uint32_t f8) {
-  volatile double q = static_cast<double>(f8) * 1e-8;
-  return static_cast<float>(q);
-}
-inline float Fraction9(uint32_t f9) {
-  volatile double q = static_cast<double>(f9) * 1e-9;
-  return static_cast<float>(q);
-}
-#endif
-
-/* 16 bytes of text starting at p, as four little-endian words */
-struct Window {
-  uint32_t x0, x1, x2, x3;
-};
-
-/* false if the aligned loads would touch memory past the chunk
-   ([p & ~3, (p & ~3) + 20) must be readable) */
-B200P_HD bool LoadWindow(const Text &t, uint32_t p, Window *w) {
-  const uint32_t a = p & ~3u;
-  if (a + 20u > t.size) return false;
-  const uint32_t w0 = Load4(t.data + a), w1 = Load4(t.data + a + 4), w2 = Load4(t.data + a + 8),
-                 w3 = Load4(t.data + a + 12), w4 = Load4(t.data + a + 16);
-  const uint32_t k = p & 3u;
-  w->x0 = BytesFrom(w0, w1, k);
-  w->x1 = BytesFrom(w1, w2, k);
-  w->x2 = BytesFrom(w2, w3, k);
-  w->x3 = BytesFrom(w3, w4, k);
-  return true;
-}
-
 /* bit 7 of every byte that is NOT an ASCII digit */
 B200P_HD uint32_t NonDigitFlags(uint32_t x) {
   const uint32_t y = x ^ 0x30303030u;
@@ -333,9 +349,10 @@ B200P_HD uint32_t Pack4(uint32_t z, uint32_t plus) {
 #endif
 }
 
-B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
+template <typename TXT>
+B200P_HD bool ToFloatWindow(const TXT &t, uint32_t p, float *out) {
   Window w;
-  if (!LoadWindow(t, p, &w)) return false;
+  if (!t.Window16(p, &w)) return false;
   const uint32_t c0 = w.x0 & 0xffu;
   if (c0 <= 0x20u) return false;           /* whitespace / control first: general code */
   const bool negative = c0 == '-';
@@ -427,7 +444,8 @@ B200P_HD bool ToFloatWindow(const Text &t, uint32_t p, float *out) {
 }
 
 /* float token at p: window fast path, else the general converter */
-B200P_HD float ToFloatFast(const Text &t, uint32_t p) {
+template <typename TXT>
+B200P_HD float ToFloatFast(const TXT &t, uint32_t p) {
   float v;
   if (ToFloatWindow(t, p, &v)) return v;
   return ToFloat(t, p, 0);
@@ -450,10 +468,10 @@ B200P_HD uint32_t PackLeading(uint32_t x, uint32_t m) {
  * strtonum.h:103-190), so overlong numbers wrap to the same value.  Tokens of 16 digits and more
  * (64-bit hashes) read two more words; 24 and more, a sign or a blank in front go to ToUint.
  */
-template <bool WIDE>
-B200P_HD bool ToUintWindow(const Text &t, uint32_t p, uint64_t *out) {
+template <bool WIDE, typename TXT>
+B200P_HD bool ToUintWindow(const TXT &t, uint32_t p, uint64_t *out) {
   Window w;
-  if (!LoadWindow(t, p, &w)) return false;
+  if (!t.Window16(p, &w)) return false;
   typedef typename std::conditional<WIDE, uint64_t, uint32_t>::type Acc;
   uint32_t flags = NonDigitFlags(w.x0);
   if (flags != 0u) {
@@ -484,10 +502,8 @@ B200P_HD bool ToUintWindow(const Text &t, uint32_t p, uint64_t *out) {
     return true;
   }
   /* 16 digits and more: bytes 16..23 of the token */
-  const uint32_t a = p & ~3u, k = p & 3u;
-  if (a + 28u > t.size) return false;
-  const uint32_t w4 = Load4(t.data + a + 16), w5 = Load4(t.data + a + 20), w6 = Load4(t.data + a + 24);
-  const uint32_t x4 = BytesFrom(w4, w5, k), x5 = BytesFrom(w5, w6, k);
+  uint32_t x4, x5;
+  if (!t.Tail8(p, &x4, &x5)) return false;
   v = static_cast<Acc>(v * 10000u + Pack4(w.x3 & 0x0f0f0f0fu, 0u));                            /* 16 digits */
   flags = NonDigitFlags(x4);
   if (flags != 0u) {
@@ -503,8 +519,8 @@ B200P_HD bool ToUintWindow(const Text &t, uint32_t p, uint64_t *out) {
   return true;
 }
 
-template <bool WIDE>
-B200P_HD uint64_t ToUintFast(const Text &t, uint32_t p, bool *negative) {
+template <bool WIDE, typename TXT>
+B200P_HD uint64_t ToUintFast(const TXT &t, uint32_t p, bool *negative) {
   uint64_t v;
   if (ToUintWindow<WIDE>(t, p, &v)) return v;
   return ToUint<WIDE>(t, p, negative);

@@ -51,6 +51,7 @@ enum ErrorBits {
   kErrValueCount = 2u,      /* reference row_block.h:177 offset.back()==value.size()||empty */
   kErrCapacity = 4u,        /* output buffers too small: host grows them and re-runs pass 2 */
   kErrInternal = 8u,        /* checked build only: a queue or output index left its bounds */
+  kErrFallback = 16u,       /* one-launch kernel (tile_kernels.cuh) gave up: parse the chunk with the two-pass walk */
 };
 
 /*
@@ -397,12 +398,20 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
  * of a line positions 1,2 are label, weight (libsvm_parser.h:50-61); everything after that is
  * consumed in groups of 2 (index[:value]) or 3 (field:index[:value]).
  */
-template <int FMT, typename IdxT, bool EMIT, bool QID>
-__device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &txt,
-                                           WarpScratch<FMT> &ws, WalkState<IdxT> &st, uint32_t head,
-                                           uint32_t count, int lane) {
+struct GroupRoles {
+  uint32_t m_label, m_weight, m_index, m_value, m_qid, m_field; /* bit i = token i of the group */
+  uint32_t at;          /* this lane's token: byte position */
+  uint32_t qid_at;      /* this lane's token, when it is a qid number: the byte after "qid:" */
+  int next_pos;         /* chain context handed to the next group */
+  bool next_first;
+};
+
+template <int FMT, bool QID>
+__device__ __forceinline__ GroupRoles TokenRoles(const Text &txt, const uint32_t *tokens,
+                                                 uint32_t head, uint32_t count, int lane,
+                                                 int carry_pos, bool carry_first) {
   const bool active = lane < count;
-  const uint32_t entry = active ? ws.tokens[head + lane] : 3u;
+  const uint32_t entry = active ? tokens[head + lane] : 3u;
   const uint32_t at = entry >> 2;
   const uint32_t kind = entry & 3u;   /* separator kind, see SeparatorKind() */
 
@@ -442,8 +451,8 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
     const uint32_t line_m = __ballot_sync(0xffffffffu, active && kind == 3u);
     const uint32_t bound_m = __ballot_sync(0xffffffffu, active && kind == 1u);
     const uint32_t start_m = act_m & ~bound_m;                    /* chain position 1 */
-    const uint32_t c1 = st.carry_pos == 1 ? 1u : 0u, c2 = st.carry_pos == 2 ? 1u : 0u;
-    const uint32_t c3 = st.carry_pos >= 3 ? 1u : 0u, cf = st.carry_first ? 1u : 0u;
+    const uint32_t c1 = carry_pos == 1 ? 1u : 0u, c2 = carry_pos == 2 ? 1u : 0u;
+    const uint32_t c3 = carry_pos >= 3 ? 1u : 0u, cf = carry_first ? 1u : 0u;
     const uint32_t p2 = bound_m & ((start_m << 1) | c1);          /* chain position 2 */
     const uint32_t p3 = bound_m & ((p2 << 1) | c2);               /* chain position 3 */
     const uint32_t p4 = bound_m & ((p3 << 1) | c3);               /* longer chains */
@@ -551,14 +560,14 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
       pos = lane - j + 1;
       first = (nl_m >> j) & 1u;
     } else {
-      pos = st.carry_pos + lane + 1;
-      first = st.carry_first;
+      pos = carry_pos + lane + 1;
+      first = carry_first;
     }
     prev_pos = __shfl_up_sync(0xffffffffu, pos, 1);
     int prev_first = __shfl_up_sync(0xffffffffu, static_cast<int>(first), 1);
     if (lane == 0) {
-      prev_pos = st.carry_pos;
-      prev_first = st.carry_first;
+      prev_pos = carry_pos;
+      prev_first = carry_first;
     }
     bool is_label = false, is_weight = false, is_index = false, is_value = false, is_field = false;
     if (active) {
@@ -595,6 +604,33 @@ __device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &tx
     next_pos = __shfl_sync(0xffffffffu, pos, last);
     next_first = __shfl_sync(0xffffffffu, static_cast<int>(first), last) != 0;
   }
+
+  GroupRoles r;
+  r.m_label = m_label;
+  r.m_weight = m_weight;
+  r.m_index = m_index;
+  r.m_value = m_value;
+  r.m_qid = m_qid;
+  r.m_field = m_field;
+  r.at = at;
+  r.qid_at = qid_at;
+  r.next_pos = next_pos;
+  r.next_first = next_first;
+  return r;
+}
+
+/* The roles of one group, then (EMIT) into the role queues of the two-pass walk. */
+template <int FMT, typename IdxT, bool EMIT, bool QID>
+__device__ __forceinline__ void TokenGroup(const WalkParams &prm, const Text &txt,
+                                           WarpScratch<FMT> &ws, WalkState<IdxT> &st, uint32_t head,
+                                           uint32_t count, int lane) {
+  const GroupRoles roles = TokenRoles<FMT, QID>(txt, ws.tokens, head, count, lane, st.carry_pos,
+                                                st.carry_first);
+  const uint32_t m_label = roles.m_label, m_weight = roles.m_weight, m_index = roles.m_index;
+  const uint32_t m_value = roles.m_value, m_qid = roles.m_qid, m_field = roles.m_field;
+  const uint32_t at = roles.at, qid_at = roles.qid_at;
+  const int next_pos = roles.next_pos;
+  const bool next_first = roles.next_first;
 
   if (EMIT) {
     const uint32_t lt = LaneMaskLt();
