@@ -27,7 +27,7 @@ EXPORTS = (
     "b200p_set_host_threads", "b200p_copied_bytes", "b200p_next_to", "b200p_host_alloc",
     "b200p_host_free",
     "b200p_set_profiling", "b200p_kernel_time", "b200p_version", "b200p_parse_device_noalloc",
-    "b200p_block_max",
+    "b200p_block_max", "b200p_current_device", "b200p_device_count",
 )
 
 

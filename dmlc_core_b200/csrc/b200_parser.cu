@@ -31,10 +31,12 @@
 
 namespace b200p {
 
-__global__ void ZeroLabels(float *label, const ChunkSummary *summary, unsigned long long cap) {
-  /* CSV rows without a label column keep label 0.0f (reference csv_parser.h:77) */
-  unsigned long long rows = summary->total[kRows];
-  if (rows > cap) rows = cap;
+__global__ void ZeroLabels(float *label, const ChunkSummary *summary, unsigned long long cap,
+                           unsigned long long cap_nnz) {
+  /* CSV rows without a label column keep label 0.0f (reference csv_parser.h:77).  Like pass 2,
+     writes nothing when the arrays cannot hold the chunk. */
+  const unsigned long long rows = summary->total[kRows];
+  if (rows > cap || summary->total[kNnz] > cap_nnz) return;
   for (unsigned long long i = blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x;
        i < rows; i += static_cast<unsigned long long>(gridDim.x) * blockDim.x) {
     label[i] = 0.0f;
@@ -557,7 +559,7 @@ static int EnqueueTiles(b200p_handle h, Slot *s) {
 static int EnqueueEmit(b200p_handle h, Slot *s) {
   const WalkParams p = MakeParams(h, *s);
   if (h->cfg.format == B200P_FORMAT_CSV) {
-    ZeroLabels<<<296, 256, 0, s->stream>>>(s->dev.label, s->d_summary, s->dev.cap_rows);
+    ZeroLabels<<<296, 256, 0, s->stream>>>(s->dev.label, s->d_summary, s->dev.cap_rows, s->dev.cap_nnz);
     ++h->launches;
   }
   ProfBegin(h, B200P_KERNEL_EMIT, s->stream);
@@ -790,6 +792,24 @@ const char *b200p_version(void) { return "dmlc_b200 0.1 sm_100a checked"; }
 const char *b200p_version(void) { return "dmlc_b200 0.1 sm_100a"; }
 #endif
 
+int b200p_current_device(void) {
+  int d = -1;
+  if (cudaGetDevice(&d) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  return d;
+}
+
+int b200p_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
 const char *b200p_last_error(b200p_handle h) {
   if (h == NULL) return g_create_error.c_str();
   static thread_local std::string mine; /* a copy: the other thread may fail while this one reads */
@@ -932,11 +952,18 @@ int b200p_parse_device_async(b200p_handle h, const void *d_text, uint64_t nbytes
   if ((reinterpret_cast<uintptr_t>(d_text) & 15u) != 0) return Fail(h, B200P_E_INVALID, "device chunk must be 16-byte aligned");
   DeviceScope on_device(h->cfg.device);
   CUDA_TRY(h, on_device.status());
+  if (h->resident_pending) {
+    /* one chunk per finish: the handle has one set of result arrays for this path, a second
+       chunk would overwrite the first one's rows and its error bits would never be looked at */
+    return Fail(h, B200P_E_AGAIN, "b200p_parse_device_async: a chunk is pending, call b200p_parse_device_finish first");
+  }
   Slot *s = &h->resident;
   s->text = static_cast<const uint8_t *>(d_text);
   s->nbytes = nbytes;
   h->resident_pending = true;
-  return EnqueueParse(h, s);
+  const int rc = EnqueueParse(h, s);
+  if (rc != B200P_OK) h->resident_pending = false;
+  return rc;
 }
 
 int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out) {
@@ -1496,7 +1523,7 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
   ScanTiles<<<p.num_tiles, kScanTile, 0, stream>>>(p.counts, p.num_ranges, p.tile_base, p.num_tiles);
   ScanFinish<<<1, kScanTile, 0, stream>>>(p.tile_base, p.num_tiles, p.num_ranges, &scratch->summary);
   if (rq->format == B200P_FORMAT_CSV) {
-    ZeroLabels<<<296, 256, 0, stream>>>(p.label, &scratch->summary, p.cap_rows);
+    ZeroLabels<<<296, 256, 0, stream>>>(p.label, &scratch->summary, p.cap_rows, p.cap_nnz);
   }
   LaunchWalkPlain(rq->format, wide, p, stream, true);
   NOALLOC_TRY(cudaGetLastError());
@@ -1519,6 +1546,10 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
                     "%llu entries", sum.total[kRows], sum.total[kNnz]);
     }
     return B200P_E_CAPACITY;
+  }
+  if (sum.error & kErrInternal) {
+    NoAllocSay(errbuf, errlen, "internal consistency check failed (checked build): a queue or output index left its bounds");
+    return B200P_E_CUDA;
   }
   if (sum.error & kErrNegativeIndex) {
     NoAllocSay(errbuf, errlen, "Check failed: sign == true (negative value in an unsigned index/field)");

@@ -25,6 +25,7 @@
 #include <exception>
 #include <functional>
 #include <limits>
+#include <memory>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -55,16 +56,25 @@ static int EnvInt(const char *name, int fallback) {
   return (v != NULL && *v != '\0') ? std::atoi(v) : fallback;
 }
 
-/* DMLC_B200_DEVICE: a CUDA ordinal (one process per GPU, the usual launch), or "auto" =
-   part_index modulo DMLC_B200_NUM_DEVICES (default 8), for a single process that opens one
-   parser per part and wants them spread over the GPUs of the box. */
+/* Which GPU a parser runs on.
+   DMLC_B200_DEVICE = a CUDA ordinal, or "auto" = part_index modulo DMLC_B200_NUM_DEVICES
+   (default 8), for a single process that opens one parser per part and wants them spread over
+   the GPUs of the box.  Without the variable: the device that is current on the calling thread
+   (a host program that called cudaSetDevice(k) gets its blocks parsed on GPU k); a process that
+   has not touched CUDA yet but was started by a launcher gets LOCAL_RANK. */
 static int DeviceFor(unsigned part_index) {
   const char *v = std::getenv("DMLC_B200_DEVICE");
   if (v != NULL && std::strcmp(v, "auto") == 0) {
     const int n = std::max(1, EnvInt("DMLC_B200_NUM_DEVICES", 8));
     return static_cast<int>(part_index % static_cast<unsigned>(n));
   }
-  return EnvInt("DMLC_B200_DEVICE", 0);
+  if (v != NULL && *v != '\0') return std::atoi(v);
+  const int current = b200p_current_device();
+  if (current > 0) return current;
+  const int local = EnvInt("LOCAL_RANK", -1);
+  const int count = b200p_device_count();
+  if (local >= 0 && count > 0) return local % count;
+  return std::max(0, current);
 }
 
 /*
@@ -130,7 +140,11 @@ class B200TextParser : public Parser<IndexType> {
     feeder_error_ = nullptr;
     b200p_rowblock dropped;
     while (b200p_pending(handle_) > 0) {
-      if (b200p_next(handle_, &dropped) != B200P_OK) break;
+      /* b200p_next takes the chunk off the queue before it looks at it, so a chunk that fails
+         to parse is gone all the same: keep draining, or the blocks behind it would come out
+         at the head of the next pass.  Only a CUDA failure stops the loop. */
+      const int rc = b200p_next(handle_, &dropped);
+      if (rc == B200P_E_CUDA || rc == B200P_E_INVALID) break;
     }
     source_->BeforeFirst();
     exhausted_ = false;
@@ -431,6 +445,27 @@ Parser<IndexType> *CreateParserImpl(const char *uri, unsigned part_index, unsign
  * pages (a multi-GB std::vector spends most of its append time in 4 KiB first-touch faults),
  * grown geometrically unless Reserve was told the final size.
  */
+/* bytes one in-memory load may keep pinned (see InMemoryRowIter::Init) */
+static size_t PinBudgetBytes() {
+  const int mb = EnvInt("DMLC_B200_ITER_PIN_MB", -1);
+  if (mb >= 0) return static_cast<size_t>(mb) << 20;
+  size_t avail_kb = 0;
+  if (std::FILE *f = std::fopen("/proc/meminfo", "r")) {
+    char line[256];
+    while (std::fgets(line, sizeof(line), f) != NULL) {
+      unsigned long long kb = 0;
+      if (std::sscanf(line, "MemAvailable: %llu kB", &kb) == 1) {
+        avail_kb = static_cast<size_t>(kb);
+        break;
+      }
+    }
+    std::fclose(f);
+  }
+  if (avail_kb == 0) return static_cast<size_t>(8) << 30;
+  const int ranks = std::max(1, EnvInt("LOCAL_WORLD_SIZE", 1));
+  return (avail_kb << 10) / 4 / static_cast<size_t>(ranks);
+}
+
 template <typename T>
 class HugeArray {
  public:
@@ -539,8 +574,16 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
         if (first && direct) {
           /* DMLC_B200_ITER_NO_PIN: behave like a host that refuses to pin (ordinary memory) */
           const bool may_pin = std::getenv("DMLC_B200_ITER_NO_PIN") == NULL;
-          const std::function<void *(size_t)> pinned = [gpu, may_pin](size_t bytes) {
-            return may_pin ? gpu->HostAlloc(bytes) : static_cast<void *>(NULL);
+          /* Pinned pages are unswappable and no rlimit caps them, so the arrays of one load pin
+             at most DMLC_B200_ITER_PIN_MB (default: a quarter of MemAvailable, divided between
+             the local ranks); what does not fit is ordinary memory -- the copies into it go
+             through the driver's staging, slower, nothing else changes. */
+          std::shared_ptr<size_t> budget(new size_t(PinBudgetBytes()));
+          const std::function<void *(size_t)> pinned = [gpu, may_pin, budget](size_t bytes) {
+            if (!may_pin || bytes > *budget) return static_cast<void *>(NULL);
+            void *p = gpu->HostAlloc(bytes);
+            if (p != NULL) *budget -= bytes;
+            return p;
           };
           offset_.UsePinned(pinned);
           label_.UsePinned(pinned);

@@ -91,6 +91,12 @@ int b200p_create(const b200p_config *config, b200p_handle *out);
 /* Replaces: delete parser (src/data/text_parser.h:37-39). */
 void b200p_destroy(b200p_handle h);
 
+/* The CUDA device current on the calling thread (-1 without a usable GPU) and the number of
+   devices: lets a host layer that does not link the CUDA runtime default to "the GPU my caller
+   selected". No reference counterpart. */
+int b200p_current_device(void);
+int b200p_device_count(void);
+
 /* Text of the last failure on this handle ("" if none). h may be NULL for create failures. */
 const char *b200p_last_error(b200p_handle h);
 
@@ -101,6 +107,8 @@ const char *b200p_last_error(b200p_handle h);
  * Replaces: TextParserBase::FillData + ParseBlock on one chunk (src/data/text_parser.h:93-134).
  * b200p_parse_device = b200p_parse_device_async + b200p_parse_device_finish.
  * The async half only enqueues the kernels on the handle's stream and never synchronises.
+ * One chunk per finish: a second b200p_parse_device_async before the finish returns
+ * B200P_E_AGAIN (use several handles, one stream each, to keep several chunks in flight).
  */
 int b200p_parse_device(b200p_handle h, const void *d_text, uint64_t nbytes, b200p_rowblock *out);
 int b200p_parse_device_async(b200p_handle h, const void *d_text, uint64_t nbytes);

@@ -14,6 +14,14 @@ from oracle.pyoracle import same_rowblocks
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=["tiles", "two-pass"])
+def kernel_path(request, monkeypatch):
+    """Both kernel paths behind the same entry points: the one-launch ParseTiles kernel (default)
+    and the count / scan / emit walk it falls back to (B200P_TILES=0 is read by b200p_create)."""
+    monkeypatch.setenv("B200P_TILES", "1" if request.param == "tiles" else "0")
+    return request.param
+
+
 def _parser(cuda_lib, fmt, ib=4, lc=-1, **kw):
     from dmlc_core_b200 import Parser
     return Parser(fmt, index_bytes=ib, label_column=lc, **kw)
@@ -32,7 +40,7 @@ def _gpu_result(parser, text, path):
 
 @pytest.mark.parametrize("path", ["device", "host"])
 @pytest.mark.parametrize("case", golden_cases(), ids=lambda c: c["name"])
-def test_golden(cuda_lib, case, path):
+def test_golden(cuda_lib, case, path, kernel_path):
     text, exp = load_golden(case)
     for rb in (512, 0):
         p = _parser(cuda_lib, case["format"], case["index_bytes"], case["label_column"], range_bytes=rb)
@@ -68,7 +76,7 @@ def _random_text(rnd, nlines):
 
 
 @pytest.mark.parametrize("fmt,ib", [("libsvm", 4), ("libsvm", 8), ("libfm", 4), ("libfm", 8), ("csv", 4)])
-def test_adversarial_fuzz(cuda_lib, oracle, fmt, ib):
+def test_adversarial_fuzz(cuda_lib, oracle, fmt, ib, kernel_path):
     """Random separators / odd tokens / CRLF / qid / chains, small and multi-range inputs.
     The trailing-colon-at-end-of-line form is excluded: the reference reads past the line there
     (declared malformed); every other quirk must match, including which inputs throw."""
@@ -104,7 +112,7 @@ CORPORA = [("libsvm", "libsvm", 4, -1), ("csv", "csv", 4, 0), ("libfm", "libfm",
 
 
 @pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA)
-def test_corpus_device(cuda_lib, oracle, kind, fmt, ib, lc):
+def test_corpus_device(cuda_lib, oracle, kind, fmt, ib, lc, kernel_path):
     """The five BASELINE.json corpus shapes, a few MB each, at several range sizes."""
     from dmlc_core_b200 import datagen
     data, rows = datagen.generate(kind, 5, 3 << 20)
@@ -120,7 +128,7 @@ def test_corpus_device(cuda_lib, oracle, kind, fmt, ib, lc):
 
 
 @pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA[:4])
-def test_corpus_streaming(cuda_lib, oracle, kind, fmt, ib, lc):
+def test_corpus_streaming(cuda_lib, oracle, kind, fmt, ib, lc, kernel_path):
     """b200p_submit / b200p_next with several chunks in flight; chunks cut at line ends.
     The concatenation over chunks equals the oracle on the whole text (SURVEY 8a contract)."""
     from dmlc_core_b200 import datagen
@@ -173,7 +181,7 @@ def test_max_index_is_reduced_on_the_gpu(cuda_lib, oracle, kind, fmt, ib, lc):
     p.close()
 
 
-def test_edge_inputs(cuda_lib, oracle):
+def test_edge_inputs(cuda_lib, oracle, kernel_path):
     cases = [
         ("libsvm", b""), ("libsvm", b"\n"), ("libsvm", b"\n\n\r\n"), ("libsvm", b"1"), ("libsvm", b"1 2:3"),
         ("libsvm", b"1 2:3\n0 4:5"), ("libsvm", b"   \n1 1:1\n"), ("csv", b""), ("csv", b"\n\n"),
@@ -211,7 +219,7 @@ def test_errors_are_reported_like_the_reference(cuda_lib):
 
 @pytest.mark.parametrize("kind,fmt,ib,lc", [("csv", "csv", 4, 0), ("libsvm", "libsvm", 4, -1),
                                             ("libfm", "libfm", 8, -1), ("libsvm_qid", "libsvm", 4, -1)])
-def test_full_size_properties(cuda_lib, oracle, kind, fmt, ib, lc):
+def test_full_size_properties(cuda_lib, oracle, kind, fmt, ib, lc, kernel_path):
     """Size-independent checks at the largest chunk the ABI takes (1 GiB, device-resident):
     tiling a block k times must give k copies of that block's rows, offsets shifted by the block's
     nnz; and the first copy is the oracle's answer on one block."""
@@ -490,3 +498,75 @@ def test_next_to_lands_blocks_in_caller_memory(cuda_lib, oracle, kind, fmt, ib, 
         p.host_free(ptr)
     p.close()
     assert same_rowblocks(got, exp) is None
+
+
+def test_one_launch_kernel_hands_over_what_it_does_not_take(cuda_lib, oracle):
+    """ParseTiles gives up on a chunk with a line longer than its staged overhang, or with text
+    denser than its token queues; the chunk is then parsed by the two-pass kernels, and after two
+    such chunks the handle stays with them.  Results are the oracle's either way; the launch count
+    shows which kernels ran (one launch per chunk for ParseTiles, four or five for the walk)."""
+    from gpu_util import parse_on_device
+    plain = (b"1 " + b" ".join(b"%d:%d.5" % (i, i) for i in range(1, 40)) + b"\n") * 400
+    long_line = b"1 " + b" ".join(b"%d:%d.25" % (i, i) for i in range(1, 9000)) + b"\n" + plain
+    dense = (b"1 " + b"7 " * 3000 + b"\n") * 30
+    p = _parser(cuda_lib, "libsvm", 4, -1)
+    counts = []
+    for text in (plain, long_line, plain, dense, plain):
+        before = p.launch_count()
+        got = parse_on_device(p, text)
+        counts.append(p.launch_count() - before)
+        assert same_rowblocks(got, oracle.parse_buffer("libsvm", text, 4, -1)) is None
+    p.close()
+    assert counts[0] == 1 and counts[2] == 1       # ParseTiles alone
+    assert counts[1] >= 5 and counts[3] >= 5       # ParseTiles, then count / scan / emit
+    assert counts[4] >= 4                          # two strikes: the handle stays on the walk
+    # CSV rows longer than a tile are not a problem (fields, not lines, are what a warp owns)
+    wide = (b",".join(b"%d.5" % i for i in range(20000)) + b"\n") * 3
+    p = _parser(cuda_lib, "csv", 4, 0)
+    before = p.launch_count()
+    got = parse_on_device(p, wide)
+    assert p.launch_count() - before == 1
+    assert same_rowblocks(got, oracle.parse_buffer("csv", wide, 4, 0)) is None
+    # a label in a later column goes to the two-pass kernels without a detour
+    p.close()
+    p = _parser(cuda_lib, "csv", 4, 2)
+    before = p.launch_count()
+    got = parse_on_device(p, wide)
+    assert p.launch_count() - before >= 4
+    assert same_rowblocks(got, oracle.parse_buffer("csv", wide, 4, 2)) is None
+    p.close()
+
+
+@pytest.mark.parametrize("fmt,ib,lc", [("libsvm", 4, -1), ("libfm", 8, -1), ("csv", 4, 0), ("csv", 4, -1)])
+def test_tile_boundaries(cuda_lib, oracle, fmt, ib, lc):
+    """Chunk sizes around the tile / sub-range / 16-byte edges of the one-launch kernel, with
+    short rows (many row starts per sub-range) and rows that span sub-ranges."""
+    rnd = random.Random(5)
+    for sub in (512, 2048):
+        p = _parser(cuda_lib, fmt, ib, lc, range_bytes=sub)
+        tile = 8 * sub
+        for target in (1, 15, 16, 17, sub - 1, sub, sub + 1, tile - 16, tile - 1, tile, tile + 1, tile + 17,
+                       3 * tile - 5, 3 * tile + sub + 3):
+            rows = []
+            size = 0
+            while size < target:
+                n = rnd.choice([0, 1, 2, 5, 40, 300])
+                if fmt == "csv":
+                    row = ",".join("%.5g" % rnd.uniform(-50, 50) for _ in range(n + 1))
+                elif fmt == "libfm":
+                    row = "%d " % rnd.randint(0, 1) + " ".join(
+                        "%d:%d:%.4g" % (rnd.randint(0, 30), rnd.randint(0, 1 << 40), rnd.random()) for _ in range(n))
+                else:
+                    row = "%d " % rnd.randint(0, 1) + " ".join(
+                        "%d:%.4g" % (rnd.randint(0, 10 ** 6), rnd.random()) for _ in range(n))
+                rows.append(row + "\n")
+                size += len(rows[-1])
+            text = "".join(rows).encode()[:target]
+            if fmt != "csv" and text.rstrip(b"\n").endswith(b":"):
+                text = text[:-1]          # "idx:" at the very end is outside the parity contract
+            if fmt == "csv":
+                text = text.rstrip(b" ")
+            exp = oracle.parse_buffer(fmt, text, ib, lc)
+            got = _gpu_result(p, text, "device")
+            assert same_rowblocks(got, exp) is None, (fmt, sub, target)
+        p.close()

@@ -61,7 +61,7 @@ def _as_numpy(blk, pool, ib):
 
 @pytest.mark.parametrize("kind,fmt,ib,lc", [("libsvm_qid", "libsvm", 4, -1), ("libfm", "libfm", 8, -1),
                                             ("csv", "csv", 4, 0)])
-def test_noalloc_matches_parse_device_twice(cuda_lib, kind, fmt, ib, lc):
+def test_noalloc_matches_parse_device_twice(cuda_lib, oracle, kind, fmt, ib, lc):
     import torch
     from dmlc_core_b200 import Parser, capi, datagen
     from gpu_util import parse_on_device
@@ -72,6 +72,9 @@ def test_noalloc_matches_parse_device_twice(cuda_lib, kind, fmt, ib, lc):
     ref_parser = Parser(fmt, index_bytes=ib, label_column=lc)
     expected = [parse_on_device(ref_parser, t) for t in texts]
     ref_parser.close()
+    # the existing entry point is itself pinned to the CPU oracle on these very chunks
+    for t, e in zip(texts, expected):
+        assert same_rowblocks(e, oracle.parse_buffer(fmt, t.tobytes(), ib, lc)) is None
 
     rows = max(len(e["label"]) for e in expected)
     nnz = max(len(e["index"]) for e in expected)
@@ -104,3 +107,9 @@ def test_noalloc_limits_are_reported(cuda_lib):
     rc, blk, msg = capi.parse_device_noalloc(_request(capi, torch, "libsvm", 4, -1, t, pool, 4, 4))
     assert rc == capi.E_CAPACITY and blk.rows == 16 and blk.nnz == 48, msg
     assert int(pool["index"][0].item()) == -1
+    # the same for CSV, whose labels are cleared by a kernel of their own before pass 2
+    data = np.frombuffer(b"1,2,3\n4,5,6\n" * 8, dtype=np.uint8)
+    t = torch.from_numpy(data.copy()).cuda()
+    rc, blk, msg = capi.parse_device_noalloc(_request(capi, torch, "csv", 4, -1, t, pool, 4, 4))
+    assert rc == capi.E_CAPACITY and blk.rows == 16 and blk.nnz == 48, msg
+    assert float(pool["label"][0].item()) == -1.0 and float(pool["value"][0].item()) == -1.0
