@@ -27,7 +27,7 @@ EXPORTS = (
     "b200p_set_host_threads", "b200p_copied_bytes", "b200p_next_to", "b200p_host_alloc",
     "b200p_host_free",
     "b200p_set_profiling", "b200p_kernel_time", "b200p_version", "b200p_parse_device_noalloc",
-    "b200p_block_max", "b200p_current_device", "b200p_device_count",
+    "b200p_block_max", "b200p_current_device", "b200p_device_count", "b200p_set_delivery",
 )
 
 
@@ -38,7 +38,8 @@ class ParseError(RuntimeError):
 class Config(C.Structure):
     _fields_ = [("format", C.c_int32), ("index_bytes", C.c_int32), ("label_column", C.c_int32),
                 ("device", C.c_int32), ("chunk_bytes", C.c_uint64), ("range_bytes", C.c_int32),
-                ("depth", C.c_int32), ("stream", C.c_void_p)]
+                ("depth", C.c_int32), ("stream", C.c_void_p), ("out_residency", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 class RowBlock(C.Structure):
@@ -112,6 +113,12 @@ def load():
     lib.b200p_set_host_threads.restype = C.c_int
     lib.b200p_copied_bytes.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.b200p_copied_bytes.restype = C.c_int
+    lib.b200p_set_delivery.argtypes = [H, C.c_int]
+    lib.b200p_set_delivery.restype = C.c_int
+    lib.b200p_current_device.argtypes = []
+    lib.b200p_current_device.restype = C.c_int
+    lib.b200p_device_count.argtypes = []
+    lib.b200p_device_count.restype = C.c_int
     lib.b200p_block_max.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.b200p_block_max.restype = C.c_int
     lib.b200p_launch_count.argtypes = [H]
@@ -145,7 +152,7 @@ class Parser(object):
     """
 
     def __init__(self, fmt, index_bytes=4, label_column=-1, device=0, chunk_bytes=0,
-                 range_bytes=0, depth=0, stream=None):
+                 range_bytes=0, depth=0, stream=None, out_device=False):
         self.lib = load()
         cfg = Config()
         cfg.format = FORMATS.get(fmt, fmt)
@@ -156,6 +163,7 @@ class Parser(object):
         cfg.range_bytes = range_bytes
         cfg.depth = depth
         cfg.stream = stream
+        cfg.out_residency = 1 if out_device else 0
         self.index_dtype = np.uint64 if index_bytes == 8 else np.uint32
         self.index_bytes = index_bytes
         self.handle = C.c_void_p()
@@ -183,6 +191,10 @@ class Parser(object):
         if rc == E_PARSE:
             raise ParseError(msg)
         raise RuntimeError("libdmlc_b200 error %d: %s" % (rc, msg))
+
+    def set_delivery(self, on_demand):
+        """b200p_set_delivery: False = arrays come home as soon as a chunk is parsed (default)."""
+        self._check(self.lib.b200p_set_delivery(self.handle, 1 if on_demand else 0))
 
     # ---- device-resident path -------------------------------------------------------------
     def parse_device_async(self, d_ptr, nbytes):

@@ -79,6 +79,10 @@ struct Slot {
   cudaEvent_t offsets_home; /* streaming path: offset[] has reached the host (created on first use) */
   unsigned char *h_narrow;  /* pinned landing place of the one-byte LibFM field ids */
   uint64_t narrow_cap;
+  /* streaming path: what the completion thread has done with the chunk in flight */
+  int stage;                /* 0 idle, 1 handed to the completion thread, 2 finished */
+  int done_rc;              /* result of FinishParse (+ delivery) */
+  bool delivered;           /* the arrays are already in the slot's pinned host mirrors */
   Slot() { std::memset(this, 0, sizeof(*this)); }
 };
 
@@ -119,7 +123,18 @@ struct b200p_parser_s {
      drains (b200p_next / b200p_pending / b200p_block_max).  `mu` guards the slot bookkeeping
      (slots' busy flags, in_flight, lent_slot, returned_slot, the density estimate); it is never
      held across a wait for a chunk in flight.  err_mu guards `error`, prof_mu one profiling bracket. */
-  std::mutex mu, err_mu, prof_mu;
+  std::mutex mu, err_mu, prof_mu, deliver_mu;
+  /* Streaming path, third thread (internal): finishes chunks in submission order as soon as
+     their summary is home -- re-runs with larger arrays, hand-over to the two-pass kernels,
+     error bits -- and, unless delivery is on demand or the results stay on the GPU, starts the
+     device-to-host copies right away, so that they run while the consumer is still busy with
+     the previous block (the reference's parse thread runs ahead of its consumer the same way,
+     src/data/parser.h:73-82). */
+  std::thread completer;
+  bool completer_running, completer_stop;
+  std::deque<int> to_complete;
+  std::condition_variable cv_work, cv_done;
+  int delivery;              /* B200P_DELIVER_* */
   unsigned long long *d_max; /* two words for b200p_block_max, allocated on first use */
   std::atomic<bool> saw_qids; /* a LibSVM chunk reported qids: later launches use the QID kernels */
   /* one-launch kernel (ParseTiles): used while the input suits it; a chunk it gives up on is
@@ -127,7 +142,8 @@ struct b200p_parser_s {
      with the two-pass kernels */
   std::atomic<bool> use_tiles;
   std::atomic<int> tile_fallbacks;
-  uint32_t sub_bytes, over_bytes, pool_div;
+  uint32_t sub_bytes, over_bytes;
+  std::atomic<uint32_t> pool_div;
   int host_threads;          /* b200p_set_host_threads; 0 = column ids always come from the GPU */
   HostPool *pool;            /* created on first use */
   std::vector<uint64_t> iota; /* 0, 1, 2, ... in the handle's index width */
@@ -142,6 +158,12 @@ struct b200p_parser_s {
 };
 
 static thread_local std::string g_create_error;
+
+extern "C" {
+static void CompleterLoop(b200p_handle h);
+static void StopCompleter(b200p_handle h);
+static int DeliverBlock(b200p_handle h, b200p::Slot *s, const b200p::Arrays &to, uint64_t base);
+}
 
 /* Every entry point works on its handle's device but leaves the caller's current device as it
    found it (the host program may be driving other GPUs from the same thread). */
@@ -499,8 +521,9 @@ static TileParams MakeTileParams(const b200p_handle h, const Slot &s) {
   /* queue capacities per warp.  CSV: a sub-range cannot start more than sub_bytes / 2 fields.
      LibSVM / LibFM: the lines a warp owns may run into the overhang; text denser than about one
      token per four bytes sends the chunk to the two-pass kernels. */
-  p.cap_pool = h->cfg.format == B200P_FORMAT_CSV ? p.sub_bytes / 2u : std::max(256u, p.sub_bytes / h->pool_div);
-  p.cap_rows = h->cfg.format == B200P_FORMAT_CSV ? std::max(64u, p.sub_bytes / 8u) : std::max(64u, p.sub_bytes / 16u);
+  const uint32_t div = h->pool_div;      /* 4: ordinary text; 2: after a chunk proved denser (FinishParse) */
+  p.cap_pool = h->cfg.format == B200P_FORMAT_CSV ? p.sub_bytes / 2u : std::max(256u, p.sub_bytes / div);
+  p.cap_rows = std::max(64u, p.sub_bytes / (h->cfg.format == B200P_FORMAT_CSV ? 2u * div : 4u * div));
   p.scratch = s.d_tiles;
   p.summary = s.d_summary;
   p.offset = s.dev.offset;
@@ -650,7 +673,11 @@ static int FinishParse(b200p_handle h, Slot *s) {
     /* the one-launch kernel met something it does not take (a line longer than its overhang,
        text denser than its queues): this chunk goes through the two-pass kernels, and a handle
        that keeps meeting such chunks stops trying */
-    if (++h->tile_fallbacks >= kTileStrikes) h->use_tiles = false;
+    if ((sum.error & kErrDense) != 0u && h->pool_div > 2u) {
+      h->pool_div = 2u;      /* short tokens or short rows: larger queues (fewer resident CTAs) from the next chunk on */
+    } else if (++h->tile_fallbacks >= kTileStrikes) {
+      h->use_tiles = false;
+    }
     const int rc = EnqueueTwoPass(h, s);
     if (rc != B200P_OK) return rc;
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
@@ -839,6 +866,10 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
   h->slots.reserve(static_cast<size_t>(h->depth) + 2);
   h->lent_slot = -1;
   h->returned_slot = -1;
+  h->completer_running = false;
+  h->completer_stop = false;
+  h->delivery = B200P_DELIVER_EAGER;
+  if (h->cfg.out_residency != B200P_OUT_DEVICE) h->cfg.out_residency = B200P_OUT_HOST;
   h->last_block = NULL;
   h->resident_pending = false;
   h->rows_per_byte = h->nnz_per_byte = 0.0;
@@ -911,6 +942,7 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
 
 void b200p_destroy(b200p_handle h) {
   if (h == NULL) return;
+  StopCompleter(h);
   DeviceScope on_device(h->cfg.device);
   ProfCollect(h);
   for (size_t i = 0; i < h->slots.size(); ++i) DestroySlot(&h->slots[i]);
@@ -1146,7 +1178,62 @@ int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes) {
   const int rc = EnqueueParse(h, s);
   if (rc != B200P_OK) return rc;
   s->busy = true;
+  s->stage = 1;
+  s->delivered = false;
   h->in_flight.push_back(id);
+  h->to_complete.push_back(id);
+  if (!h->completer_running) {
+    h->completer_stop = false;
+    h->completer = std::thread(CompleterLoop, h);
+    h->completer_running = true;
+  }
+  h->cv_work.notify_one();
+  return B200P_OK;
+}
+
+/* the completion thread: see b200p_parser_s */
+static void CompleterLoop(b200p_handle h) {
+  DeviceScope on_device(h->cfg.device);
+  std::unique_lock<std::mutex> lk(h->mu);
+  for (;;) {
+    h->cv_work.wait(lk, [h] { return h->completer_stop || !h->to_complete.empty(); });
+    if (h->completer_stop) break;
+    const int id = h->to_complete.front();
+    h->to_complete.pop_front();
+    Slot *s = &h->slots[id];   /* slots never moves: reserved for depth + 2 entries at creation */
+    const bool deliver = h->delivery == B200P_DELIVER_EAGER && h->cfg.out_residency == B200P_OUT_HOST;
+    lk.unlock();
+    int rc = FinishParse(h, s);
+    bool delivered = false;
+    if (rc == B200P_OK && deliver && s->nbytes != 0) {
+      const ChunkSummary &sum = *s->h_summary;
+      rc = EnsureArrays(h, &s->host, sum.total[kRows], sum.total[kNnz], true);
+      if (rc == B200P_OK) rc = DeliverBlock(h, s, s->host, 0);
+      delivered = rc == B200P_OK;
+    }
+    lk.lock();
+    s->done_rc = rc;
+    s->delivered = delivered;
+    s->stage = 2;
+    h->cv_done.notify_all();
+  }
+}
+
+static void StopCompleter(b200p_handle h) {
+  {
+    std::lock_guard<std::mutex> g(h->mu);
+    if (!h->completer_running) return;
+    h->completer_stop = true;
+  }
+  h->cv_work.notify_all();
+  h->completer.join();
+  h->completer_running = false;
+}
+
+int b200p_set_delivery(b200p_handle h, int mode) {
+  if (h == NULL || (mode != B200P_DELIVER_EAGER && mode != B200P_DELIVER_ON_DEMAND)) return B200P_E_INVALID;
+  std::lock_guard<std::mutex> g(h->mu);
+  h->delivery = mode;
   return B200P_OK;
 }
 
@@ -1162,6 +1249,7 @@ int b200p_pending(b200p_handle h) {
  * column ids / LibFM field ids, and a final synchronisation.  `base` is added to every offset.
  */
 static int DeliverBlock(b200p_handle h, Slot *s, const Arrays &to, uint64_t base) {
+  std::lock_guard<std::mutex> one_at_a_time(h->deliver_mu);   /* the host pool and its tables are shared */
   const ChunkSummary &sum = *s->h_summary;
   const uint64_t rows = sum.total[kRows], nnz = sum.total[kNnz];
   {
@@ -1257,13 +1345,32 @@ static int DeliverBlock(b200p_handle h, Slot *s, const Arrays &to, uint64_t base
   return B200P_OK;
 }
 
+/* copy a block the completion thread already brought home into the caller's arrays */
+static void CopyDelivered(const b200p_handle h, const Slot &s, const Arrays &to, uint64_t base) {
+  const ChunkSummary &sum = *s.h_summary;
+  const uint64_t rows = sum.total[kRows], nnz = sum.total[kNnz];
+  const size_t iw = h->cfg.index_bytes;
+  if (rows == 0) return;
+  for (uint64_t i = 0; i <= rows; ++i) to.offset[i] = s.host.offset[i] + base;
+  std::memcpy(to.label, s.host.label, rows * 4);
+  if (sum.total[kWeights] != 0) std::memcpy(to.weight, s.host.weight, sum.total[kWeights] * 4);
+  if (sum.total[kQids] != 0) std::memcpy(to.qid, s.host.qid, sum.total[kQids] * 8);
+  if (nnz != 0) {
+    std::memcpy(to.index, s.host.index, nnz * iw);
+    if (h->cfg.format == B200P_FORMAT_LIBFM) std::memcpy(to.field, s.host.field, nnz * iw);
+  }
+  if (sum.total[kValues] != 0) std::memcpy(to.value, s.host.value, sum.total[kValues] * 4);
+}
+
 int b200p_next(b200p_handle h, b200p_rowblock *out) {
   if (h == NULL || out == NULL) return B200P_E_INVALID;
   DeviceScope on_device(h->cfg.device);
   CUDA_TRY(h, on_device.status());
   Slot *s = NULL;
+  int rc = B200P_OK;
+  bool delivered = false;
   {
-    std::lock_guard<std::mutex> g(h->mu);
+    std::unique_lock<std::mutex> lk(h->mu);
     if (h->in_flight.empty()) return Fail(h, B200P_E_EMPTY, "b200p_next: nothing submitted");
     const int id = h->in_flight.front();
     h->in_flight.pop_front();
@@ -1273,10 +1380,19 @@ int b200p_next(b200p_handle h, b200p_rowblock *out) {
        that a concurrent b200p_submit cannot pick the slot being finished here */
     h->returned_slot = id;
     h->last_block = NULL;
+    h->cv_done.wait(lk, [s] { return s->stage == 2; });
+    rc = s->done_rc;
+    delivered = s->delivered;
+    s->stage = 0;
   }
-  int rc = FinishParse(h, s);
   if (rc != B200P_OK) return rc;
-  if (s->nbytes != 0) {
+  if (h->cfg.out_residency == B200P_OUT_DEVICE) {
+    /* the consumer lives on the GPU: the arrays stay where the kernels wrote them */
+    FillBlock(h, *s, s->dev, true, out);
+    h->last_block = s;
+    return B200P_OK;
+  }
+  if (s->nbytes != 0 && !delivered) {
     const ChunkSummary &sum = *s->h_summary;
     const uint64_t rows = sum.total[kRows], nnz = sum.total[kNnz];
     rc = EnsureArrays(h, &s->host, rows, nnz, true);
@@ -1293,15 +1409,22 @@ int b200p_next_to(b200p_handle h, const b200p_destination *dst, b200p_rowblock *
   if (h == NULL || dst == NULL || out == NULL) return B200P_E_INVALID;
   DeviceScope on_device(h->cfg.device);
   CUDA_TRY(h, on_device.status());
+  if (h->cfg.out_residency != B200P_OUT_HOST) {
+    return Fail(h, B200P_E_INVALID, "b200p_next_to: this handle keeps its results on the GPU (out_residency)");
+  }
   Slot *s = NULL;
   int id = -1;
+  int rc = B200P_OK;
+  bool delivered = false;
   {
-    std::lock_guard<std::mutex> g(h->mu);
+    std::unique_lock<std::mutex> lk(h->mu);
     if (h->in_flight.empty()) return Fail(h, B200P_E_EMPTY, "b200p_next_to: nothing submitted");
     id = h->in_flight.front();   /* stays queued until it is known to fit: only this thread pops */
     s = &h->slots[id];
+    h->cv_done.wait(lk, [s] { return s->stage == 2; });
+    rc = s->done_rc;
+    delivered = s->delivered;
   }
-  int rc = FinishParse(h, s);
   Arrays to;
   to.offset = reinterpret_cast<unsigned long long *>(dst->offset);
   to.label = dst->label;
@@ -1341,10 +1464,15 @@ int b200p_next_to(b200p_handle h, const b200p_destination *dst, b200p_rowblock *
     h->returned_slot = id;
     h->last_block = NULL;
   }
+  s->stage = 0;
   if (rc != B200P_OK) return rc;
   if (s->nbytes != 0) {
-    rc = DeliverBlock(h, s, to, dst->offset_base);
-    if (rc != B200P_OK) return rc;
+    if (delivered) {
+      CopyDelivered(h, *s, to, dst->offset_base);   /* brought home before the caller said where to */
+    } else {
+      rc = DeliverBlock(h, s, to, dst->offset_base);
+      if (rc != B200P_OK) return rc;
+    }
   }
   FillBlock(h, *s, to, false, out);
   h->last_block = s;           /* b200p_block_max still works: the device arrays are intact */

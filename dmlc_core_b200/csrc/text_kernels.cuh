@@ -52,6 +52,7 @@ enum ErrorBits {
   kErrCapacity = 4u,        /* output buffers too small: host grows them and re-runs pass 2 */
   kErrInternal = 8u,        /* checked build only: a queue or output index left its bounds */
   kErrFallback = 16u,       /* one-launch kernel (tile_kernels.cuh) gave up: parse the chunk with the two-pass walk */
+  kErrDense = 32u,          /* ... because a sub-range holds more tokens or rows than its queues (not: a long line) */
 };
 
 /*

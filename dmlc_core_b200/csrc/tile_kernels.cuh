@@ -342,6 +342,7 @@ struct Collected {
   uint32_t tail;       /* CSV: values after the last row start (all values when there is none) */
   bool has_row;
   bool overflow;       /* the sub-range does not fit this kernel: the chunk goes to the two-pass path */
+  bool dense;          /* ... because a queue ran full */
   uint32_t error;      /* lane-local error bits */
 };
 
@@ -362,6 +363,7 @@ __device__ __forceinline__ void CollectTokens(const TileParams &prm, const TileT
   c.tail = 0u;
   c.has_row = false;
   c.overflow = false;
+  c.dense = false;
   c.error = 0u;
   *out = c;
   if (lo >= hi) return;
@@ -459,6 +461,7 @@ __device__ __forceinline__ void CollectTokens(const TileParams &prm, const TileT
       if (c.n_index + c.n_value + 64u > prm.cap_pool || c.n_rows + 32u > prm.cap_rows ||
           (FMT == kLibFM && c.n_index + 32u > prm.cap_pool / 2u)) {
         c.overflow = true;
+        c.dense = true;
         done = true;
         break;
       }
@@ -524,6 +527,7 @@ __device__ __forceinline__ void CollectFields(const TileParams &prm, const TileT
   c.tail = 0u;
   c.has_row = false;
   c.overflow = false;
+  c.dense = false;
   c.error = 0u;
   if (lo >= hi) {
     *out = c;
@@ -557,6 +561,7 @@ __device__ __forceinline__ void CollectFields(const TileParams &prm, const TileT
     const uint32_t step_rows = __shfl_sync(0xffffffffu, both, 31) >> 16;
     if (c.n_rows + step_rows > prm.cap_rows) {   /* cap_pool >= sub_bytes / 2 always holds the fields */
       c.overflow = true;
+      c.dense = true;
       break;
     }
     uint32_t vslot = c.n_value + (both & 0xffffu) - nv;
@@ -669,7 +674,7 @@ ParseTiles(const TileParams prm) {
     sh.count[warp][kQids] = got.n_qid;
     sh.count[warp][5] = got.tail;
     sh.count[warp][6] = got.has_row ? 1u : 0u;
-    if (got.overflow) atomicOr(&sh.flags, static_cast<uint32_t>(kErrFallback));
+    if (got.overflow) atomicOr(&sh.flags, static_cast<uint32_t>(kErrFallback) | (got.dense ? static_cast<uint32_t>(kErrDense) : 0u));
   }
   __syncthreads();
 
@@ -724,7 +729,7 @@ ParseTiles(const TileParams prm) {
         sh.base[w][5] = open;
         open = sh.count[w][6] != 0u ? sh.count[w][5] : open + sh.count[w][5];
       }
-      uint32_t err = fallback ? static_cast<uint32_t>(kErrFallback) : 0u;
+      uint32_t err = fallback ? (sh.flags & (kErrFallback | kErrDense)) : 0u;
       if (!ok) err |= kErrFallback | kErrInternal;
       if (tile + 1u == prm.num_tiles) {
         /* chunk totals, and the RowBlockContainer::GetBlock consistency check (row_block.h:177) */

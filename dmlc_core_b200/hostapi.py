@@ -44,6 +44,11 @@ def load(path=None):
     lib.dmlcb_parser_bytes_read.restype = C.c_uint64
     lib.dmlcb_parser_free.argtypes = [C.c_void_p]
     lib.dmlcb_parser_free.restype = None
+    lib.dmlcb_parser_time.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_char_p, C.c_int, C.c_int,
+                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                      C.POINTER(C.c_double), C.c_char_p, C.c_uint64]
+    lib.dmlcb_parser_time.restype = C.c_double
     lib.dmlcb_rowiter_create.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_char_p, C.c_int,
                                          C.POINTER(Block), C.POINTER(C.c_uint64), C.c_char_p,
                                          C.c_uint64]
@@ -86,6 +91,26 @@ def _block_to_numpy(b, index_bytes):
         "index": _arr(b.index + base * isz if b.index else None, nnz if b.index else 0, idt),
         "value": _arr(b.value + base * 4 if b.value else None, nnz if b.value else 0, np.float32),
     }
+
+
+def time_parser(uri, part=0, nparts=1, type_="libsvm", index_bytes=4, passes=1, want_hash=False, lib=None):
+    """Parser<I>::Create(uri, part, nparts, type) drained `passes` times (BeforeFirst between
+    them), sizes only: the reference's throughput driver loop. Returns a dict with seconds
+    (Create excluded), create_seconds, rows / nnz (summed over the passes), bytes_read and, if
+    asked, the FNV-1a hashes of the seven arrays from one extra untimed pass."""
+    lib = lib if lib is not None else load()
+    rows, nnz, nbytes = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+    h = (C.c_uint64 * 7)()
+    created = C.c_double(0)
+    err = C.create_string_buffer(2048)
+    sec = lib.dmlcb_parser_time(uri.encode(), part, nparts, type_.encode(), index_bytes, passes,
+                                C.byref(rows), C.byref(nnz), C.byref(nbytes),
+                                h if want_hash else None, C.byref(created), err, 2048)
+    if sec < 0:
+        raise DmlcError(err.value.decode())
+    return {"seconds": float(sec), "create_seconds": float(created.value), "rows": int(rows.value),
+            "nnz": int(nnz.value), "bytes_read": int(nbytes.value),
+            "hash": [int(x) for x in h] if want_hash else None}
 
 
 class CppParser(object):

@@ -215,6 +215,8 @@ class B200TextParser : public Parser<IndexType> {
       return kIntoDone;
     }
   }
+  /* blocks will be asked for with NextInto: their arrays travel when the destination is known */
+  void DeliverOnDemand() { b200p_set_delivery(handle_, B200P_DELIVER_ON_DEMAND); }
   /* pinned host memory that takes device-to-host copies at link speed (b200p_host_alloc) */
   void *HostAlloc(size_t bytes) {   /* NULL when the host will not pin that much */
     void *p = NULL;
@@ -546,6 +548,7 @@ class InMemoryRowIter : public RowBlockIter<IndexType> {
       bool first = true;
       double t_next = 0, t_append = 0, t_max = 0;   /* DMLC_B200_ITER_TRACE: where the load went */
       const bool direct = gpu != NULL && std::getenv("DMLC_B200_ITER_COPY") == NULL;
+      if (direct) gpu->DeliverOnDemand();
       for (;;) {
         double ta = GetTime();
         if (direct && !first) {

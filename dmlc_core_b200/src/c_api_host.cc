@@ -6,6 +6,9 @@
  */
 #include <dmlc/data.h>
 #include <dmlc/io.h>
+#include <random>   /* the reference's header (drop-in build) uses std::mt19937 without including it */
+#include <dmlc/input_split_shuffle.h>
+#include <dmlc/timer.h>
 
 #include <cstdio>
 #include <cstring>
@@ -41,6 +44,51 @@ static void Export(const dmlc::RowBlock<I> &b, dmlcb_block *out) {
   out->field = b.field;
   out->index = b.index;
   out->value = b.value;
+}
+
+/* FNV-1a over the bytes of one array, carried across blocks */
+static inline uint64_t Fnv(uint64_t h, const void *data, size_t nbytes) {
+  const unsigned char *p = static_cast<const unsigned char *>(data);
+  for (size_t i = 0; i < nbytes; ++i) h = (h ^ p[i]) * 1099511628211ull;
+  return h;
+}
+
+template <typename I>
+static void DrainTimed(dmlc::Parser<I> *p, int passes, int hash_first, uint64_t *rows, uint64_t *nnz,
+                       uint64_t *hash7, double *seconds) {
+  uint64_t r = 0, z = 0;
+  if (hash_first) {
+    /* one untimed pass hashing label, weight, qid, field, index, value and the row lengths:
+       independent of how the rows are cut into blocks */
+    for (int k = 0; k < 7; ++k) hash7[k] = 14695981039346656037ull;
+    while (p->Next()) {
+      const dmlc::RowBlock<I> &b = p->Value();
+      const size_t base = b.offset[0], n = b.offset[b.size] - base;
+      for (size_t i = 0; i < b.size; ++i) {
+        const uint64_t len = b.offset[i + 1] - b.offset[i];
+        hash7[0] = Fnv(hash7[0], &len, 8);
+      }
+      hash7[1] = Fnv(hash7[1], b.label, b.size * sizeof(float));
+      if (b.weight != NULL) hash7[2] = Fnv(hash7[2], b.weight, b.size * sizeof(float));
+      if (b.qid != NULL) hash7[3] = Fnv(hash7[3], b.qid, b.size * sizeof(uint64_t));
+      if (b.field != NULL) hash7[4] = Fnv(hash7[4], b.field + base, n * sizeof(I));
+      if (b.index != NULL) hash7[5] = Fnv(hash7[5], b.index + base, n * sizeof(I));
+      if (b.value != NULL) hash7[6] = Fnv(hash7[6], b.value + base, n * sizeof(float));
+    }
+    p->BeforeFirst();
+  }
+  const double t0 = dmlc::GetTime();
+  for (int k = 0; k < passes; ++k) {
+    if (k != 0) p->BeforeFirst();
+    while (p->Next()) {
+      const dmlc::RowBlock<I> &v = p->Value();
+      r += v.size;
+      z += v.offset[v.size] - v.offset[0];
+    }
+  }
+  *seconds = dmlc::GetTime() - t0;
+  *rows = r;
+  *nnz = z;
 }
 
 extern "C" {
@@ -103,6 +151,50 @@ void dmlcb_parser_free(void *handle) {
   delete h->p64;
   delete h->p32;
   delete h;
+}
+
+/*
+ * Parser<I>::Create(uri, part, nparts, type) drained `passes` times with BeforeFirst between the
+ * passes, touching only sizes -- the loop of the reference's throughput drivers
+ * (test/libsvm_parser_test.cc:14-34, test/csv_parser_test.cc:22-57).  Returns the seconds the
+ * passes took (Create not included), or -1 with a message.  hash7 (optional): FNV-1a of the
+ * seven arrays over one extra, untimed pass, for comparing two implementations on one file.
+ */
+double dmlcb_parser_time(const char *uri, unsigned part, unsigned nparts, const char *type,
+                         int index_bytes, int passes, uint64_t *rows, uint64_t *nnz,
+                         uint64_t *bytes_read, uint64_t *hash7, double *create_seconds,
+                         char *err, uint64_t errlen) {
+  double seconds = -1.0;
+  try {
+    const double t0 = dmlc::GetTime();
+    if (index_bytes == 8) {
+      dmlc::Parser<uint64_t> *p = dmlc::Parser<uint64_t>::Create(uri, part, nparts, type);
+      if (create_seconds != NULL) *create_seconds = dmlc::GetTime() - t0;
+      try {
+        DrainTimed(p, passes, hash7 != NULL, rows, nnz, hash7, &seconds);
+        *bytes_read = p->BytesRead();
+      } catch (...) {
+        delete p;
+        throw;
+      }
+      delete p;
+    } else {
+      dmlc::Parser<uint32_t> *p = dmlc::Parser<uint32_t>::Create(uri, part, nparts, type);
+      if (create_seconds != NULL) *create_seconds = dmlc::GetTime() - t0;
+      try {
+        DrainTimed(p, passes, hash7 != NULL, rows, nnz, hash7, &seconds);
+        *bytes_read = p->BytesRead();
+      } catch (...) {
+        delete p;
+        throw;
+      }
+      delete p;
+    }
+  } catch (const std::exception &e) {
+    Say(err, errlen, e.what());
+    return -1.0;
+  }
+  return seconds;
 }
 
 /* RowBlockIter<I>::Create + NumCol (reference test/dataiter_test.cc); blocks come from
@@ -193,6 +285,32 @@ uint64_t dmlcb_split_bytes(const char *uri, unsigned part, unsigned nparts, int 
     return ~0ull;
   }
   if (pieces != NULL) *pieces = n;
+  return total;
+}
+
+/*
+ * InputSplitShuffle::Create(uri, part, nparts, "text", num_shuffle_parts, seed) drained with
+ * NextChunk over `passes` passes (BeforeFirst between them): the bytes in the order they come
+ * out, for comparing the sub-partition order with the reference's for a fixed seed.
+ */
+uint64_t dmlcb_shuffle_bytes(const char *uri, unsigned part, unsigned nparts, unsigned shuffle_parts,
+                             int seed, int passes, char *buf, uint64_t cap, char *err, uint64_t errlen) {
+  uint64_t total = 0;
+  try {
+    dmlc::InputSplit *split = dmlc::InputSplitShuffle::Create(uri, part, nparts, "text", shuffle_parts, seed);
+    dmlc::InputSplit::Blob blob;
+    for (int k = 0; k < passes; ++k) {
+      if (k != 0) split->BeforeFirst();
+      while (split->NextChunk(&blob)) {
+        if (total + blob.size <= cap) std::memcpy(buf + total, blob.dptr, blob.size);
+        total += blob.size;
+      }
+    }
+    delete split;
+  } catch (const std::exception &e) {
+    Say(err, errlen, e.what());
+    return ~0ull;
+  }
   return total;
 }
 

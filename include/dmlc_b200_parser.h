@@ -56,7 +56,14 @@ typedef struct b200p_config {
   int32_t range_bytes;   /* bytes of text one warp owns (0 = default); tuning only */
   int32_t depth;         /* chunks in flight for b200p_submit/b200p_next (0 = 3) */
   void *stream;          /* cudaStream_t for the device-resident calls; NULL = own stream */
+  int32_t out_residency; /* b200p_submit / b200p_next: B200P_OUT_HOST (0, default) returns the arrays
+                            in pinned host memory; B200P_OUT_DEVICE leaves them in HBM for a consumer
+                            that lives on the GPU (no device-to-host copy at all) */
+  int32_t reserved;      /* 0 */
 } b200p_config;
+
+#define B200P_OUT_HOST 0
+#define B200P_OUT_DEVICE 1
 
 /*
  * One parsed chunk.  Field for field the RowBlock<IndexType> of include/dmlc/data.h:169-231
@@ -126,7 +133,8 @@ int b200p_parse_device_finish(b200p_handle h, b200p_rowblock *out);
  *                       where they lie; caller-pinned memory must stay untouched until the
  *                       matching b200p_next), or pageable memory (staged through the pinned
  *                       buffer first).
- *   b200p_next          wait for the oldest submitted chunk; pointers are pinned host memory,
+ *   b200p_next          wait for the oldest submitted chunk; pointers are pinned host memory
+ *                       (device memory for B200P_OUT_DEVICE handles, out->on_device == 1),
  *                       valid until the next b200p_next / b200p_destroy on this handle.
  * Replaces: ParserImpl::ParseNext -> FillData (src/data/parser.h:30-44, text_parser.h:93-134).
  *
@@ -141,6 +149,21 @@ int b200p_submit(b200p_handle h, const void *text, uint64_t nbytes);
 int b200p_next(b200p_handle h, b200p_rowblock *out);
 /* chunks submitted and not yet returned by b200p_next */
 int b200p_pending(b200p_handle h);
+
+/*
+ * When the arrays of a chunk travel to the host (B200P_OUT_HOST handles).
+ *   B200P_DELIVER_EAGER      (default) as soon as the chunk's kernels have finished, into the
+ *                            slot's own pinned arrays, by a thread inside the library: the copies
+ *                            run while the caller is still working on the previous block, and
+ *                            b200p_next only waits for them.  This is the reference's ThreadedParser
+ *                            running ahead of its consumer (src/data/parser.h:73-82).
+ *   B200P_DELIVER_ON_DEMAND  when b200p_next / b200p_next_to is called: for b200p_next_to users,
+ *                            whose destination is not known before the call (a block that was
+ *                            already brought home eagerly is copied on from the slot's arrays).
+ */
+#define B200P_DELIVER_EAGER 0
+#define B200P_DELIVER_ON_DEMAND 1
+int b200p_set_delivery(b200p_handle h, int mode);
 
 /*
  * b200p_next with the arrays written straight into memory of the caller's choosing, at the

@@ -229,5 +229,19 @@ class Reference(_Checker):
         return {"seconds": float(sec), "rows": int(rows.value), "nnz": int(nnz.value),
                 "bytes": int(nbytes.value)}
 
+    def hash_uri(self, uri, part=0, nparts=1, type_="libsvm", index_bytes=4, nthread=0):
+        """FNV-1a of the seven arrays (row lengths for offset) of one drain -> (list of 7, rows, nnz)."""
+        h = (C.c_uint64 * 7)()
+        rows, nnz = C.c_uint64(0), C.c_uint64(0)
+        self.lib.refshim_hash_uri.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_char_p, C.c_int, C.c_int,
+                                              C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                              C.POINTER(C.c_uint64)]
+        self.lib.refshim_hash_uri.restype = C.c_int
+        rc = self.lib.refshim_hash_uri(uri.encode(), part, nparts, type_.encode(), index_bytes, nthread,
+                                       h, C.byref(rows), C.byref(nnz))
+        if rc != 0:
+            raise RuntimeError("refshim_hash_uri failed")
+        return [int(x) for x in h], int(rows.value), int(nnz.value)
+
     def max_threads(self):
         return int(self.lib.refshim_max_threads())

@@ -21,6 +21,8 @@
  */
 #include <dmlc/data.h>
 #include <dmlc/io.h>
+#include <random>   /* the reference header uses std::mt19937 without including it */
+#include <dmlc/input_split_shuffle.h>
 #include <dmlc/omp.h>
 #include <dmlc/timer.h>
 
@@ -189,6 +191,32 @@ void IterUri(const char *uri, unsigned part, unsigned nparts, const char *type,
 
 }  // namespace
 
+static inline uint64_t ShimFnv(uint64_t h, const void *data, size_t nbytes) {
+  const unsigned char *p = static_cast<const unsigned char *>(data);
+  for (size_t i = 0; i < nbytes; ++i) h = (h ^ p[i]) * 1099511628211ull;
+  return h;
+}
+template <typename I>
+static void ShimHash(dmlc::Parser<I> *p, uint64_t *hash7, uint64_t *rows, uint64_t *nnz) {
+  for (int k = 0; k < 7; ++k) hash7[k] = 14695981039346656037ull;
+  while (p->Next()) {
+    const dmlc::RowBlock<I> &b = p->Value();
+    const size_t base = b.offset[0], n = b.offset[b.size] - base;
+    for (size_t i = 0; i < b.size; ++i) {
+      const uint64_t len = b.offset[i + 1] - b.offset[i];
+      hash7[0] = ShimFnv(hash7[0], &len, 8);
+    }
+    hash7[1] = ShimFnv(hash7[1], b.label, b.size * sizeof(float));
+    if (b.weight != NULL) hash7[2] = ShimFnv(hash7[2], b.weight, b.size * sizeof(float));
+    if (b.qid != NULL) hash7[3] = ShimFnv(hash7[3], b.qid, b.size * sizeof(uint64_t));
+    if (b.field != NULL) hash7[4] = ShimFnv(hash7[4], b.field + base, n * sizeof(I));
+    if (b.index != NULL) hash7[5] = ShimFnv(hash7[5], b.index + base, n * sizeof(I));
+    if (b.value != NULL) hash7[6] = ShimFnv(hash7[6], b.value + base, n * sizeof(float));
+    *rows += b.size;
+    *nnz += n;
+  }
+}
+
 extern "C" {
 
 void refshim_parse_uri(const char *uri, unsigned part, unsigned nparts, const char *type,
@@ -275,6 +303,54 @@ uint64_t refshim_split_bytes(const char *uri, unsigned part, unsigned nparts, ch
   delete split;
   if (nchunks != NULL) *nchunks = n;
   return total;
+}
+
+/* FNV-1a of the seven arrays of Parser<I>::Create(uri, ...) drained once (row lengths instead of
+   offsets, so the hash does not depend on how rows are cut into blocks): bench.py compares it
+   with the same hash taken through the B200 parser on the same file. Returns 0, or -1 on error. */
+/* reference InputSplitShuffle (include/dmlc/input_split_shuffle.h) drained with NextChunk over
+   `passes` passes: the bytes in the order they come out */
+uint64_t refshim_shuffle_bytes(const char *uri, unsigned part, unsigned nparts, unsigned shuffle_parts,
+                               int seed, int passes, char *buf, uint64_t cap) {
+  uint64_t total = 0;
+  try {
+    dmlc::InputSplit *split = dmlc::InputSplitShuffle::Create(uri, part, nparts, "text", shuffle_parts, seed);
+    dmlc::InputSplit::Blob blob;
+    for (int k = 0; k < passes; ++k) {
+      if (k != 0) split->BeforeFirst();
+      while (split->NextChunk(&blob)) {
+        if (total + blob.size <= cap) std::memcpy(buf + total, blob.dptr, blob.size);
+        total += blob.size;
+      }
+    }
+    delete split;
+  } catch (const std::exception &e) {
+    std::fprintf(stderr, "refshim_shuffle_bytes: %s\n", e.what());
+    return ~0ull;
+  }
+  return total;
+}
+
+int refshim_hash_uri(const char *uri, unsigned part, unsigned nparts, const char *type,
+                     int index_bytes, int nthread, uint64_t *hash7, uint64_t *rows, uint64_t *nnz) {
+  if (nthread > 0) omp_set_num_threads(nthread);
+  *rows = 0;
+  *nnz = 0;
+  try {
+    if (index_bytes == 8) {
+      dmlc::Parser<uint64_t> *p = dmlc::Parser<uint64_t>::Create(uri, part, nparts, type);
+      ShimHash(p, hash7, rows, nnz);
+      delete p;
+    } else {
+      dmlc::Parser<uint32_t> *p = dmlc::Parser<uint32_t>::Create(uri, part, nparts, type);
+      ShimHash(p, hash7, rows, nnz);
+      delete p;
+    }
+  } catch (const std::exception &e) {
+    std::fprintf(stderr, "refshim_hash_uri: %s\n", e.what());
+    return -1;
+  }
+  return 0;
 }
 
 /* Timed drain, touching only sizes (test/libsvm_parser_test.cc:21-33 semantics).

@@ -137,6 +137,31 @@ def test_long_line_and_error_propagation(hostapi, oracle, tmp_path, monkeypatch)
     p.close()
 
 
+def test_rewind_after_a_parse_error_starts_from_the_top(hostapi, tmp_path, monkeypatch):
+    """Two chunks that each hold a negative index are in flight when Next() throws for the first;
+    BeforeFirst() must drop both, so that the next pass begins with the file's first block again
+    and not with what was queued behind the failure."""
+    monkeypatch.setenv("DMLC_B200_CHUNK_MB", "1")
+    monkeypatch.setenv("DMLC_B200_DEPTH", "3")
+    good = b"".join(b"%d 1:%d 2:0.5\n" % (i % 2, i) for i in range(120000))     # ~1.7 MiB
+    bad = b"0 -2:1\n"
+    f = tmp_path / "twice_bad.svm"
+    f.write_bytes(good[:1 << 20].rsplit(b"\n", 1)[0] + b"\n" + bad + good + bad + good)
+    fresh = hostapi.CppParser(str(f), 0, 1, "libsvm", 4)
+    first = fresh.next()
+    fresh.close()
+    p = hostapi.CppParser(str(f), 0, 1, "libsvm", 4)
+    for _ in range(3):       # each pass: the first block, then the failure
+        b = p.next()
+        assert b is not None and np.array_equal(b["index"], first["index"])
+        assert np.array_equal(b["value"].view(np.uint32), first["value"].view(np.uint32))
+        with pytest.raises(hostapi.DmlcError, match="sign == true"):
+            while p.next() is not None:
+                pass
+        p.before_first()
+    p.close()
+
+
 def test_true_dropin_build_against_reference_headers(hostapi):
     """oracle/_ref/libdmlc_dropin.so = the reference's headers, InputSplit, filesystem and
     registry with src/data.cc replaced by this package's parser.

@@ -502,24 +502,27 @@ def test_next_to_lands_blocks_in_caller_memory(cuda_lib, oracle, kind, fmt, ib, 
 
 def test_one_launch_kernel_hands_over_what_it_does_not_take(cuda_lib, oracle):
     """ParseTiles gives up on a chunk with a line longer than its staged overhang, or with text
-    denser than its token queues; the chunk is then parsed by the two-pass kernels, and after two
-    such chunks the handle stays with them.  Results are the oracle's either way; the launch count
-    shows which kernels ran (one launch per chunk for ParseTiles, four or five for the walk)."""
+    denser than its token queues; the chunk is then parsed by the two-pass kernels.  Dense text
+    makes the handle switch to larger queues once; after two other such chunks it stays with the
+    two-pass kernels.  Results are the oracle's either way; the launch count shows which kernels
+    ran (one launch per chunk for ParseTiles, four more for the walk)."""
     from gpu_util import parse_on_device
-    plain = (b"1 " + b" ".join(b"%d:%d.5" % (i, i) for i in range(1, 40)) + b"\n") * 400
+    plain = (b"1 " + b" ".join(b"%d:%d.5" % (100000 + i, i) for i in range(1, 40)) + b"\n") * 400
     long_line = b"1 " + b" ".join(b"%d:%d.25" % (i, i) for i in range(1, 9000)) + b"\n" + plain
-    dense = (b"1 " + b"7 " * 3000 + b"\n") * 30
+    dense = (b"1 " + b" ".join(b"%d:1" % (i % 90) for i in range(40)) + b"\n") * 600      # ~2.5 bytes per token
+    densest = (b"1 " + b"7 " * 3000 + b"\n") * 30                                           # 2 bytes per token
     p = _parser(cuda_lib, "libsvm", 4, -1)
     counts = []
-    for text in (plain, long_line, plain, dense, plain):
+    for text in (plain, dense, dense, long_line, plain, densest, plain):
         before = p.launch_count()
         got = parse_on_device(p, text)
         counts.append(p.launch_count() - before)
         assert same_rowblocks(got, oracle.parse_buffer("libsvm", text, 4, -1)) is None
     p.close()
-    assert counts[0] == 1 and counts[2] == 1       # ParseTiles alone
-    assert counts[1] >= 5 and counts[3] >= 5       # ParseTiles, then count / scan / emit
-    assert counts[4] >= 4                          # two strikes: the handle stays on the walk
+    assert counts[0] == 1                          # ParseTiles alone
+    assert counts[1] >= 5 and counts[2] == 1       # dense: handed over once, then larger queues
+    assert counts[3] >= 5 and counts[4] == 1       # a long line: handed over (first strike)
+    assert counts[5] >= 5 and counts[6] >= 4       # second strike: the handle stays on the walk
     # CSV rows longer than a tile are not a problem (fields, not lines, are what a warp owns)
     wide = (b",".join(b"%d.5" % i for i in range(20000)) + b"\n") * 3
     p = _parser(cuda_lib, "csv", 4, 0)
@@ -570,3 +573,80 @@ def test_tile_boundaries(cuda_lib, oracle, fmt, ib, lc):
             got = _gpu_result(p, text, "device")
             assert same_rowblocks(got, exp) is None, (fmt, sub, target)
         p.close()
+
+
+@pytest.mark.parametrize("kind,fmt,ib,lc", CORPORA[:3])
+def test_host_text_in_device_csr_out(cuda_lib, oracle, kind, fmt, ib, lc):
+    """out_residency = device: b200p_submit takes host text, b200p_next hands out device pointers
+    (valid until the next b200p_next) and nothing but the 48-byte summary crosses the link back."""
+    from dmlc_core_b200 import datagen
+    data, rows = datagen.generate(kind, 21, 5 << 20)
+    raw = data.tobytes()
+    exp = oracle.parse_buffer(fmt, raw, ib, lc)
+    cuts, pos = [0], 0
+    while pos < len(raw):
+        pos = min(len(raw), pos + (800 << 10))
+        if pos < len(raw):
+            pos = raw.index(b"\n", pos) + 1
+        cuts.append(pos)
+    p = _parser(cuda_lib, fmt, ib, lc, chunk_bytes=1 << 20, depth=3, out_device=True)
+    blocks = []
+    todo = [raw[a:b] for a, b in zip(cuts[:-1], cuts[1:])]
+    n_chunks = len(todo)
+    while todo or p.pending():
+        while todo and p.pending() < 3:
+            p.submit(todo.pop(0))
+        blk = p.next_raw()
+        assert blk.on_device == 1
+        blocks.append(p.fetch(blk))          # read back through b200p_fetch, for the comparison only
+    up, down = p.copied_bytes()
+    p.close()
+    got = {k: np.concatenate([b[k] for b in blocks]) for k in ("label", "weight", "qid", "field", "index", "value")}
+    offs, run = [np.zeros(1, dtype=np.uint64)], 0
+    for b in blocks:
+        offs.append(b["offset"][1:] + np.uint64(run))
+        run += len(b["index"])
+    got["offset"] = np.concatenate(offs)
+    got["error"] = 0
+    assert same_rowblocks(got, exp) is None
+    fetched = sum(sum(v.nbytes for k, v in b.items() if k != "error" and len(v)) for b in blocks)
+    assert up == len(raw) and down <= fetched + 8 * n_chunks   # the fetches of this test, nothing else
+
+
+def test_copies_come_home_while_the_consumer_is_busy(cuda_lib, oracle):
+    """With eager delivery (the default) the device-to-host copies of block k+1 run while the
+    caller still holds block k; with delivery on demand they start inside b200p_next.  A consumer
+    that spends 5 ms per block must therefore finish sooner in the first mode."""
+    import torch
+    from dmlc_core_b200 import datagen
+    data, rows = datagen.generate("libsvm", 3, 48 << 20)
+    host = torch.from_numpy(data).pin_memory()
+    raw = host.numpy()
+    base = host.data_ptr()
+    n = raw.size
+    exp_rows = rows
+    walls = {}
+    for on_demand in (True, False, True, False):
+        p = _parser(cuda_lib, "libsvm", 4, -1, chunk_bytes=48 << 20, depth=3)
+        p.set_delivery(on_demand)
+        passes, got_rows = 12, 0
+
+        def run():
+            nonlocal got_rows
+            got_rows = 0
+            fed = 0
+            while fed < passes or p.pending():
+                while fed < passes and p.pending() < 3:
+                    p.submit_in_place(base, n)
+                    fed += 1
+                got_rows += p.next_raw().rows
+                time.sleep(0.005)
+        run()                      # warm-up: allocations, module load
+        t0 = time.perf_counter()
+        run()
+        wall = time.perf_counter() - t0
+        p.close()
+        assert got_rows == exp_rows * passes
+        walls.setdefault(on_demand, []).append(wall)
+    eager, lazy = min(walls[False]), min(walls[True])
+    assert eager < lazy - 0.004, (eager, lazy)

@@ -199,3 +199,36 @@ def test_input_split_cache_file_is_interchangeable_with_the_reference(hostapi, r
             assert lines(i_read_theirs) == lines(want)
     decorated = sorted(p.name for p in tmp_path.iterdir() if p.name.startswith("mine2"))
     assert decorated == ["mine2.split2.part0", "mine2.split2.part1"]      # URISpec's suffix, uri_spec.h:59-66
+
+
+def test_input_split_shuffle_matches_reference(reference, tmp_path):
+    """InputSplitShuffle of the stand-alone layer: for a fixed seed the sub-partitions come out in
+    the reference's order, on the first pass and after every BeforeFirst (which reshuffles)."""
+    import ctypes as C
+    from dmlc_core_b200 import build, hostapi
+    build.build_host()
+    lib = hostapi.load()
+    lib.dmlcb_shuffle_bytes.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int,
+                                        C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64]
+    lib.dmlcb_shuffle_bytes.restype = C.c_uint64
+    ref = reference.lib
+    ref.refshim_shuffle_bytes.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int,
+                                          C.c_char_p, C.c_uint64]
+    ref.refshim_shuffle_bytes.restype = C.c_uint64
+    rnd = random.Random(4)
+    files = []
+    for k in range(3):
+        f = tmp_path / ("part%d.txt" % k)
+        f.write_bytes(b"".join(b"%d %d:%d\n" % (k, i, rnd.randint(0, 10 ** rnd.randint(1, 9)))
+                               for i in range(rnd.randint(200, 900))))
+        files.append(str(f))
+    uri = ";".join(files).encode()
+    cap = 1 << 20
+    for nparts, shuffle_parts, seed in ((1, 1, 0), (1, 4, 0), (2, 3, 7), (3, 5, 123), (2, 8, 1)):
+        for part in range(nparts):
+            mine, theirs = C.create_string_buffer(cap), C.create_string_buffer(cap)
+            err = C.create_string_buffer(512)
+            n1 = lib.dmlcb_shuffle_bytes(uri, part, nparts, shuffle_parts, seed, 3, mine, cap, err, 512)
+            n2 = ref.refshim_shuffle_bytes(uri, part, nparts, shuffle_parts, seed, 3, theirs, cap)
+            assert n1 == n2 and n1 < cap, (err.value, n1, n2)
+            assert mine.raw[:n1] == theirs.raw[:n2], (nparts, shuffle_parts, seed, part)
