@@ -236,7 +236,7 @@ def reference_rate(ref, shape, path, nthread, seconds, part=0, nparts=1, passes=
     return None if "error" in got else got
 
 
-def run_reference_arm(args):
+def run_reference_arm(args, out):
     """--impl reference: the reference's own multithreaded CPU parser on this box's host cores, on
     the headline shape (and, briefly, on the other four)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -246,7 +246,8 @@ def run_reference_arm(args):
     from oracle.pyoracle import Reference
     ref = Reference.load()
     if ref is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libdmlc_ref.so missing"}))
+        out.write(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libdmlc_ref.so missing"}) + "\n")
+        out.flush()
         return
     nthread = os.cpu_count() or 1
     shape = SHAPES[args.shape]
@@ -258,16 +259,18 @@ def run_reference_arm(args):
     uri = uri_of(path, shape)
     nbytes = data.size
     del data
-    for _ in range(max(1, args.warmup)):
-        ref.time_uri(uri, 0, 1, shape["fmt"], shape["ib"], nthread=nthread, passes=1)
-    t = 0.0
-    r = None
-    for _ in range(args.steps):
-        r = ref.time_uri(uri, 0, 1, shape["fmt"], shape["ib"], nthread=nthread, passes=1)
-        t += r["seconds"]
+    # one process of its own per leg, OMP_NUM_THREADS = all host threads: the reference sizes its
+    # OpenMP team from that variable alone, and launchers (torchrun) export OMP_NUM_THREADS=1
+    got = reference_rate(ref, shape, path, nthread, 0.0, passes=args.steps)   # behind one untimed pass
     os.remove(path)
-    ms = t / args.steps * 1e3
-    value = nbytes / (t / args.steps) / GB
+    if got is None:
+        out.write(json.dumps({"impl": "reference", "unavailable": "the reference failed on the sample"}) + "\n")
+        out.flush()
+        return
+    ms = got["seconds_per_pass"] * 1e3
+    value = got["GBps"]
+    r = {"rows": got["rows"]}
+    t = got["seconds_per_pass"] * args.steps
     shapes = []
     if not args.no_shapes:
         for i, sh in enumerate(SHAPES):
@@ -299,7 +302,8 @@ def run_reference_arm(args):
     }
     if shapes:
         line["shapes"] = shapes
-    print(json.dumps(line))
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 # ------------------------------------------------------------------------------------------------
@@ -496,9 +500,27 @@ def measure_shape(torch, shape, args, local, peak, ref, nthread):
     return out
 
 
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner at
+    any NCCL_DEBUG level from VERSION up, whatever NCCL_DEBUG_FILE says), so everything that is not
+    the line goes to stderr: file descriptor 1 is pointed at stderr and the line is written to a
+    private copy of the original stdout."""
+    sys.stdout.flush()
+    keep = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(keep, "w")
+
+
 def main():
     args = parse_args()
+    out = claim_stdout()
+    # launchers export OMP_NUM_THREADS=1; the text generator (OpenMP, csrc/datagen.c) may use this
+    # rank's share of the host cores
+    ranks_here = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 1) // ranks_here))
     if args.impl == "reference":
+        run_reference_arm(args, out)
+        return
         run_reference_arm(args)
         return
     import torch
@@ -791,7 +813,8 @@ def main():
             line["cpu_sharded"] = cpu_sharded
         if shapes is not None:
             line["shapes"] = shapes
-        print(json.dumps(line))
+        out.write(json.dumps(line) + "\n")
+        out.flush()
     if world > 1:
         dist.destroy_process_group()
 

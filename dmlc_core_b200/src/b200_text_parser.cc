@@ -783,7 +783,9 @@ class CachedRowIter : public RowBlockIter<IndexType> {
 
   /* parser == NULL: the cache must already exist */
   CachedRowIter(Parser<IndexType> *parser, const std::string &cache_file)
-      : cache_file_(cache_file), fi_(NULL), num_col_(0) {
+      : cache_file_(cache_file), fi_(NULL), num_col_(0), held_(-1), next_slot_(0), loading_(false),
+        stop_(false), eof_(false) {
+    ready_[0] = ready_[1] = false;
     if (parser != NULL) {
       try {
         Build(parser);
@@ -797,36 +799,130 @@ class CachedRowIter : public RowBlockIter<IndexType> {
     CHECK(fi_ != NULL) << "failed to build cache file " << cache_file_;
     if (parser == NULL) {
       /* NumCol of an existing cache: the largest max_index over its pages */
-      while (LoadPage()) num_col_ = std::max(num_col_, static_cast<size_t>(page_max_index_) + 1);
-      BeforeFirst();
+      while (LoadPage(&pages_[0])) num_col_ = std::max(num_col_, static_cast<size_t>(pages_[0].max_index) + 1);
+      std::fseek(fi_, 0, SEEK_SET);
     }
   }
   virtual ~CachedRowIter() {
+    StopLoader();
     if (fi_ != NULL) std::fclose(fi_);
   }
-  virtual void BeforeFirst(void) { std::fseek(fi_, 0, SEEK_SET); }
+  virtual void BeforeFirst(void) {
+    StopLoader();
+    std::fseek(fi_, 0, SEEK_SET);
+    ready_[0] = ready_[1] = false;
+    held_ = -1;
+    next_slot_ = 0;
+    eof_ = false;
+  }
+  /* Pages come through a loader thread with two page buffers, so that page k+1 is read from disk
+     while the caller works on page k (the reference replays its cache through a ThreadedIter,
+     src/data/disk_row_iter.h:96-108). */
   virtual bool Next(void) {
-    if (!LoadPage()) return false;
-    block_.size = label_.size();
-    block_.offset = BeginPtr(offset_);
-    block_.label = BeginPtr(label_);
-    block_.weight = BeginPtr(weight_);
-    block_.qid = BeginPtr(qid_);
-    block_.field = BeginPtr(field_);
-    block_.index = BeginPtr(index_);
-    block_.value = BeginPtr(value_);
+    std::unique_lock<std::mutex> lk(mu_);
+    if (held_ >= 0) {          /* hand the previous page's buffer back to the loader */
+      ready_[held_] = false;
+      held_ = -1;
+      cv_.notify_all();
+    }
+    if (!loading_ && !eof_) {
+      stop_ = false;
+      loading_ = true;
+      loader_ = std::thread([this] { LoaderLoop(); });
+    }
+    const int slot = next_slot_;
+    cv_.wait(lk, [this, slot] { return ready_[slot] || eof_; });
+    if (!ready_[slot]) {
+      if (loader_error_) {
+        std::exception_ptr e = loader_error_;
+        loader_error_ = nullptr;
+        std::rethrow_exception(e);
+      }
+      return false;
+    }
+    held_ = slot;
+    next_slot_ = 1 - slot;
+    const Page &pg = pages_[slot];
+    block_.size = pg.label.size();
+    block_.offset = BeginPtr(pg.offset);
+    block_.label = BeginPtr(pg.label);
+    block_.weight = BeginPtr(pg.weight);
+    block_.qid = BeginPtr(pg.qid);
+    block_.field = BeginPtr(pg.field);
+    block_.index = BeginPtr(pg.index);
+    block_.value = BeginPtr(pg.value);
     return true;
   }
   virtual const RowBlock<IndexType> &Value(void) const { return block_; }
   virtual size_t NumCol(void) const { return num_col_; }
 
  private:
-  template <typename T>
-  static void WriteVec(std::FILE *f, const std::vector<T> &v) {
-    const uint64_t n = v.size();
-    CHECK(std::fwrite(&n, sizeof(n), 1, f) == 1) << "cache write failed";
-    if (n != 0) CHECK(std::fwrite(&v[0], sizeof(T), v.size(), f) == v.size()) << "cache write failed";
+  struct Page {
+    std::vector<size_t> offset;
+    std::vector<real_t> label, weight, value;
+    std::vector<uint64_t> qid;
+    std::vector<IndexType> field, index;
+    IndexType max_index, max_field;
+    Page() : max_index(0), max_field(0) {}
+    size_t MemCost() const {
+      return offset.size() * sizeof(size_t) + (label.size() + weight.size() + value.size()) * sizeof(real_t) +
+             qid.size() * sizeof(size_t) + (field.size() + index.size()) * sizeof(IndexType);
+    }
+    void Clear() {
+      offset.assign(1, 0);
+      label.clear(); weight.clear(); qid.clear(); field.clear(); index.clear(); value.clear();
+      max_index = 0;
+      max_field = 0;
+    }
+  };
+
+  void LoaderLoop() {
+    int slot = next_slot_;
+    try {
+      for (;;) {
+        {
+          std::unique_lock<std::mutex> lk(mu_);
+          cv_.wait(lk, [this, slot] { return stop_ || !ready_[slot]; });
+          if (stop_) break;
+        }
+        const bool got = LoadPage(&pages_[slot]);   /* the slot is free: nobody else touches it */
+        std::lock_guard<std::mutex> lk(mu_);
+        if (!got) {
+          eof_ = true;
+          cv_.notify_all();
+          break;
+        }
+        ready_[slot] = true;
+        cv_.notify_all();
+        slot = 1 - slot;
+      }
+    } catch (...) {
+      std::lock_guard<std::mutex> lk(mu_);
+      loader_error_ = std::current_exception();
+      eof_ = true;
+      cv_.notify_all();
+    }
   }
+  void StopLoader() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      if (!loading_) return;
+      stop_ = true;
+    }
+    cv_.notify_all();
+    loader_.join();
+    loading_ = false;
+  }
+
+  /* one array of a page: element count, then the elements (reference include/dmlc/serializer.h:105-112) */
+  template <typename T>
+  static void WriteArray(std::FILE *f, const T *data, size_t count) {
+    const uint64_t n = count;
+    CHECK(std::fwrite(&n, sizeof(n), 1, f) == 1) << "cache write failed";
+    if (n != 0) CHECK(std::fwrite(data, sizeof(T), count, f) == count) << "cache write failed";
+  }
+  template <typename T>
+  static void WriteVec(std::FILE *f, const std::vector<T> &v) { WriteArray(f, BeginPtr(v), v.size()); }
   template <typename T>
   static bool ReadVec(std::FILE *f, std::vector<T> *v) {
     uint64_t n = 0;
@@ -834,72 +930,100 @@ class CachedRowIter : public RowBlockIter<IndexType> {
     v->resize(static_cast<size_t>(n));
     return n == 0 || std::fread(&(*v)[0], sizeof(T), v->size(), f) == v->size();
   }
-  size_t MemCost() const {
-    return offset_.size() * sizeof(size_t) + (label_.size() + weight_.size() + value_.size()) * sizeof(real_t) +
-           qid_.size() * sizeof(size_t) + (field_.size() + index_.size()) * sizeof(IndexType);
+  void WriteTail(std::FILE *fo, IndexType max_field, IndexType max_index) {
+    CHECK(std::fwrite(&max_field, sizeof(IndexType), 1, fo) == 1) << "cache write failed";
+    CHECK(std::fwrite(&max_index, sizeof(IndexType), 1, fo) == 1) << "cache write failed";
+    num_col_ = std::max(num_col_, static_cast<size_t>(max_index) + 1);
   }
-  void ClearPage() {
-    offset_.assign(1, 0);
-    label_.clear(); weight_.clear(); qid_.clear(); field_.clear(); index_.clear(); value_.clear();
-    page_max_index_ = 0;
-    page_max_field_ = 0;
+  void SavePage(std::FILE *fo, const Page &pg) {
+    WriteVec(fo, pg.offset); WriteVec(fo, pg.label); WriteVec(fo, pg.weight); WriteVec(fo, pg.qid);
+    WriteVec(fo, pg.field); WriteVec(fo, pg.index); WriteVec(fo, pg.value);
+    WriteTail(fo, pg.max_field, pg.max_index);
   }
-  void SavePage(std::FILE *fo) {
-    WriteVec(fo, offset_); WriteVec(fo, label_); WriteVec(fo, weight_); WriteVec(fo, qid_);
-    WriteVec(fo, field_); WriteVec(fo, index_); WriteVec(fo, value_);
-    CHECK(std::fwrite(&page_max_field_, sizeof(IndexType), 1, fo) == 1) << "cache write failed";
-    CHECK(std::fwrite(&page_max_index_, sizeof(IndexType), 1, fo) == 1) << "cache write failed";
-    num_col_ = std::max(num_col_, static_cast<size_t>(page_max_index_) + 1);
+  /* a block that is a page by itself goes to the file straight from the parser's (pinned) arrays:
+     same page layout (RowBlockContainer::Save, reference src/data/row_block.h:189-201), no copy */
+  void SaveBlockAsPage(std::FILE *fo, const RowBlock<IndexType> &b, IndexType max_index, IndexType max_field) {
+    const size_t base = b.offset[0], nnz = b.offset[b.size] - base;
+    if (base == 0) {
+      WriteArray(fo, b.offset, b.size + 1);
+    } else {
+      std::vector<size_t> rebased(b.size + 1);
+      for (size_t i = 0; i <= b.size; ++i) rebased[i] = b.offset[i] - base;
+      WriteVec(fo, rebased);
+    }
+    WriteArray(fo, b.label, b.size);
+    WriteArray(fo, b.weight, b.weight != NULL ? b.size : 0);
+    WriteArray(fo, b.qid, b.qid != NULL ? b.size : 0);
+    WriteArray(fo, b.field != NULL ? b.field + base : b.field, b.field != NULL ? nnz : 0);
+    WriteArray(fo, b.index != NULL ? b.index + base : b.index, b.index != NULL ? nnz : 0);
+    WriteArray(fo, b.value != NULL ? b.value + base : b.value, b.value != NULL ? nnz : 0);
+    WriteTail(fo, max_field, max_index);
   }
-  bool LoadPage() {
-    if (!ReadVec(fi_, &offset_)) return false;
-    CHECK(ReadVec(fi_, &label_) && ReadVec(fi_, &weight_) && ReadVec(fi_, &qid_) && ReadVec(fi_, &field_) &&
-          ReadVec(fi_, &index_) && ReadVec(fi_, &value_) &&
-          std::fread(&page_max_field_, sizeof(IndexType), 1, fi_) == 1 &&
-          std::fread(&page_max_index_, sizeof(IndexType), 1, fi_) == 1)
+  bool LoadPage(Page *pg) {
+    if (!ReadVec(fi_, &pg->offset)) return false;
+    CHECK(ReadVec(fi_, &pg->label) && ReadVec(fi_, &pg->weight) && ReadVec(fi_, &pg->qid) &&
+          ReadVec(fi_, &pg->field) && ReadVec(fi_, &pg->index) && ReadVec(fi_, &pg->value) &&
+          std::fread(&pg->max_field, sizeof(IndexType), 1, fi_) == 1 &&
+          std::fread(&pg->max_index, sizeof(IndexType), 1, fi_) == 1)
         << "Bad RowBlock format";
     return true;
+  }
+  static size_t BlockCost(const RowBlock<IndexType> &b) {
+    const size_t nnz = b.offset[b.size] - b.offset[0];
+    return (b.size + 1) * sizeof(size_t) + b.size * sizeof(real_t) * (b.weight != NULL ? 2 : 1) +
+           (b.qid != NULL ? b.size * sizeof(uint64_t) : 0) +
+           nnz * (sizeof(IndexType) * (b.field != NULL ? 2 : 1) + (b.value != NULL ? sizeof(real_t) : 0));
   }
   void Build(Parser<IndexType> *parser) {
     std::FILE *fo = std::fopen(cache_file_.c_str(), "wb");
     CHECK(fo != NULL) << "cannot write cache file " << cache_file_;
     B200TextParser<IndexType> *gpu = dynamic_cast<B200TextParser<IndexType> *>(parser);
     const double t0 = GetTime();
-    ClearPage();
+    Page &acc = pages_[0];      /* small blocks are gathered here until they make a page */
+    acc.Clear();
     try {
       while (parser->Next()) {
         const RowBlock<IndexType> &b = parser->Value();
-        const size_t base = b.offset[0], nnz = b.offset[b.size] - base, shift = offset_.back();
-        label_.insert(label_.end(), b.label, b.label + b.size);
-        if (b.weight != NULL) weight_.insert(weight_.end(), b.weight, b.weight + b.size);
-        if (b.qid != NULL) qid_.insert(qid_.end(), b.qid, b.qid + b.size);
-        if (b.field != NULL) field_.insert(field_.end(), b.field + base, b.field + base + nnz);
-        index_.insert(index_.end(), b.index + base, b.index + base + nnz);
+        const size_t base = b.offset[0], nnz = b.offset[b.size] - base;
+        IndexType max_index = 0, max_field = 0;
         if (gpu != NULL) {
           uint64_t mi = 0, mf = 0;
           gpu->BlockMax(&mi, &mf);
-          page_max_index_ = std::max(page_max_index_, static_cast<IndexType>(mi));
-          page_max_field_ = std::max(page_max_field_, static_cast<IndexType>(mf));
+          max_index = static_cast<IndexType>(mi);
+          max_field = static_cast<IndexType>(mf);
         } else {
-          for (size_t i = 0; i < nnz; ++i) page_max_index_ = std::max(page_max_index_, b.index[base + i]);
+          for (size_t i = 0; i < nnz; ++i) max_index = std::max(max_index, b.index[base + i]);
           if (b.field != NULL) {
-            for (size_t i = 0; i < nnz; ++i) page_max_field_ = std::max(page_max_field_, b.field[base + i]);
+            for (size_t i = 0; i < nnz; ++i) max_field = std::max(max_field, b.field[base + i]);
           }
         }
-        if (b.value != NULL) value_.insert(value_.end(), b.value + base, b.value + base + nnz);
-        for (size_t i = 1; i <= b.size; ++i) offset_.push_back(shift + b.offset[i] - base);
-        if (MemCost() >= kPageSize) {
-          SavePage(fo);
-          ClearPage();
+        if (acc.label.empty() && BlockCost(b) >= kPageSize / 2) {
+          SaveBlockAsPage(fo, b, max_index, max_field);
+          continue;
+        }
+        const size_t shift = acc.offset.back();
+        acc.label.insert(acc.label.end(), b.label, b.label + b.size);
+        if (b.weight != NULL) acc.weight.insert(acc.weight.end(), b.weight, b.weight + b.size);
+        if (b.qid != NULL) acc.qid.insert(acc.qid.end(), b.qid, b.qid + b.size);
+        if (b.field != NULL) acc.field.insert(acc.field.end(), b.field + base, b.field + base + nnz);
+        acc.index.insert(acc.index.end(), b.index + base, b.index + base + nnz);
+        if (b.value != NULL) acc.value.insert(acc.value.end(), b.value + base, b.value + base + nnz);
+        for (size_t i = 1; i <= b.size; ++i) acc.offset.push_back(shift + b.offset[i] - base);
+        acc.max_index = std::max(acc.max_index, max_index);
+        acc.max_field = std::max(acc.max_field, max_field);
+        if (acc.MemCost() >= kPageSize) {
+          SavePage(fo, acc);
+          acc.Clear();
         }
       }
-      if (!label_.empty()) SavePage(fo);
+      if (!acc.label.empty()) SavePage(fo, acc);
     } catch (...) {
       std::fclose(fo);
       std::remove(cache_file_.c_str());
       throw;
     }
     std::fclose(fo);
+    acc.Clear();
     const double dt = GetTime() - t0;
     LOG(INFO) << "finish reading at " << (parser->BytesRead() >> 20UL) / (dt > 0 ? dt : 1e-9) << " MB/sec";
   }
@@ -907,12 +1031,16 @@ class CachedRowIter : public RowBlockIter<IndexType> {
   std::string cache_file_;
   std::FILE *fi_;
   size_t num_col_;
-  IndexType page_max_index_, page_max_field_;
   RowBlock<IndexType> block_;
-  std::vector<size_t> offset_;
-  std::vector<real_t> label_, weight_, value_;
-  std::vector<uint64_t> qid_;
-  std::vector<IndexType> field_, index_;
+  Page pages_[2];
+  /* loader thread state, under mu_ */
+  std::mutex mu_;
+  std::condition_variable cv_;
+  std::thread loader_;
+  bool ready_[2];
+  int held_, next_slot_;
+  bool loading_, stop_, eof_;
+  std::exception_ptr loader_error_;
 };
 
 /* reference CreateIter_, src/data.cc:87-107: "#cachefile" selects the disk-backed iterator.
