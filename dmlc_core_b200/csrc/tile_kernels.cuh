@@ -388,6 +388,13 @@ __device__ __forceinline__ void CollectTokens(const TileParams &prm, const TileT
   const uint32_t lt = LaneMaskLt();
   const uint32_t me = 1u << lane;
   const uint8_t *const my_win = tt.win + 16u * lane - tt.win_lo;   /* my_win + base = my 16 bytes */
+  /* the role queues as offsets (in entries) from the pool: they are carved from one block */
+  uint16_t *const q16 = q.pool;
+  const uint32_t o_pool = 0u;
+  const uint32_t o_row_at = static_cast<uint32_t>(q.row_at - q.pool), o_row_nnz = static_cast<uint32_t>(q.row_nnz - q.pool);
+  const uint32_t o_weight = static_cast<uint32_t>(q.weight - q.pool), o_qid = static_cast<uint32_t>(q.qid - q.pool);
+  const uint32_t o_field = static_cast<uint32_t>(q.field - q.pool);
+  const uint32_t room_pool = prm.cap_pool - 64u, room_rows = prm.cap_rows - 32u, room_field = prm.cap_pool / 2u - 32u;
 
   for (uint32_t base = begin & ~uint32_t(kStepBytes - 1); !done; base += kStepBytes) {
     if (base + kStepBytes > tt.win_hi) {
@@ -458,37 +465,45 @@ __device__ __forceinline__ void CollectTokens(const TileParams &prm, const TileT
     while (fill - head >= 32u || (done && fill > head)) {
       const uint32_t count = min(fill - head, 32u);
       /* room for one more group in every queue?  (warp-uniform) */
-      if (c.n_index + c.n_value + 64u > prm.cap_pool || c.n_rows + 32u > prm.cap_rows ||
-          (FMT == kLibFM && c.n_index + 32u > prm.cap_pool / 2u)) {
+      if (c.n_index + c.n_value > room_pool || c.n_rows > room_rows ||
+          (FMT == kLibFM && c.n_index > room_field)) {
         c.overflow = true;
         c.dense = true;
         done = true;
         break;
       }
       const GroupRoles r = TokenRoles<FMT, QID>(tt.global, q.tokens, head, count, lane, carry_pos, carry_first);
-      /* every token has at most one role: one store per lane, into the queue of its role
-         (index entries grow from the front of the pool, value entries from its back) */
+      /* every token has at most one role: one store per lane, into the queue of its role (index
+         entries grow from the front of the pool, value entries from its back).  The queues are
+         addressed as offsets into the warp's one block of 16-bit entries. */
       const uint32_t rel = r.at - tt.win_lo;
       const bool is_index = (r.m_index & me) != 0u, is_value = (r.m_value & me) != 0u;
       const bool is_label = (r.m_label & me) != 0u, is_weight = (r.m_weight & me) != 0u;
       const uint32_t mine = is_index ? r.m_index : (is_value ? r.m_value : (is_label ? r.m_label : r.m_weight));
       const uint32_t rank = __popc(mine & lt);
-      uint16_t *dst = is_index ? q.pool + c.n_index + rank
-                               : (is_value ? q.pool + (prm.cap_pool - 1u - c.n_value) - rank
-                                           : (is_label ? q.row_at + c.n_rows + rank : q.weight + c.n_weight + rank));
-      if (is_index || is_value || is_label || is_weight) *dst = static_cast<uint16_t>(rel);
-      if (is_label) q.row_nnz[c.n_rows + rank] = static_cast<uint16_t>(c.n_index + __popc(r.m_index & lt));
+      const uint32_t at_index = o_pool + c.n_index + rank;
+      const uint32_t at_value = o_pool + (prm.cap_pool - 1u - c.n_value) - rank;
+      const uint32_t at_label = o_row_at + c.n_rows + rank;
+      const uint32_t at_weight = o_weight + c.n_weight + rank;
+      const uint32_t slot16 = is_index ? at_index : (is_value ? at_value : (is_label ? at_label : at_weight));
+      if (is_index || is_value || is_label || is_weight) q16[slot16] = static_cast<uint16_t>(rel);
+      if (is_label) q16[o_row_nnz + c.n_rows + rank] = static_cast<uint16_t>(c.n_index + __popc(r.m_index & lt));
       if (FMT == kLibFM) {
         /* a field id is converted before the reference knows whether the triple is kept
-           (libfm_parser.h:73), so a '-' raises even on a token that is then dropped */
-        if ((r.m_field & me) != 0u && tt.byte(r.at) == '-') c.error |= kErrNegativeIndex;
+           (libfm_parser.h:73), so a '-' raises even on a token that is then dropped.  Kept field
+           tokens are converted later and report it there; only the dropped ones (no index token
+           behind them; the group's last token may be one) are looked at here. */
+        const uint32_t maybe_dropped = r.m_field & ~(r.m_index >> 1);
+        if (maybe_dropped != 0u) {
+          if ((maybe_dropped & me) != 0u && tt.byte(r.at) == '-') c.error |= kErrNegativeIndex;
+        }
         uint32_t prev_at = __shfl_up_sync(0xffffffffu, r.at, 1);
         if (lane == 0) prev_at = carry_at;
-        if (is_index) q.field[c.n_index + rank] = static_cast<uint16_t>(prev_at - tt.win_lo);
+        if (is_index) q16[o_field + c.n_index + rank] = static_cast<uint16_t>(prev_at - tt.win_lo);
       }
       if (FMT == kLibSVM && r.m_qid != 0u) {
         if ((r.m_qid & me) != 0u) {
-          q.qid[c.n_qid + __popc(r.m_qid & lt)] = static_cast<uint16_t>(r.qid_at - tt.win_lo);
+          q16[o_qid + c.n_qid + __popc(r.m_qid & lt)] = static_cast<uint16_t>(r.qid_at - tt.win_lo);
         }
         c.n_qid += __popc(r.m_qid);
       }
