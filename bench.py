@@ -465,8 +465,8 @@ def measure_shape(torch, shape, args, local, peak, ref, nthread):
     out = {"config": shape["key"], "what": shape["what"], "named_size_GB": shape["gb"],
            "measured_on_bytes": n, "rows": int(blk.rows), "nnz": int(blk.nnz),
            "value": n / (ms * 1e-3) / GB, "unit": "GB/s", "ms_per_pass": ms,
-           "kernel_ms": {"count": kms[0], "scan": kms[1], "parse_or_emit": kms[2]},
-           "one_launch_kernel": kms[0] == 0.0,
+           "kernel_ms": {"collect_or_count": kms[0], "scan": kms[1], "convert_or_parse_or_emit": kms[2]},
+           "path": {0: "two-pass walk", 1: "one launch (ParseTiles)", 2: "collect / scan / convert"}[db.lanes[0][0].last_path()],
            "roofline": {"bound": "hbm", "algorithmic_bytes": int(b_alg),
                         "dominant_kernel_frac": b_alg / (dominant * 1e-3) / GB / peak if dominant else None,
                         "all_kernels_frac": b_alg / (total_k * 1e-3) / GB / peak if total_k else None,
@@ -615,8 +615,12 @@ def main():
     total_ms = sum(kms)
     achieved = b_alg / (dominant_ms * 1e-3) / GB
     fmt_id = {"libsvm": 0, "libfm": 1, "csv": 2}[shape["fmt"]]
-    kernel_name = ("ParseTiles<%d, %s" % (fmt_id, "unsigned long" if ib == 8 else "unsigned int")) \
-        if kms[0] == 0.0 else "WalkText<%d, %s, 1" % (fmt_id, "unsigned long" if ib == 8 else "unsigned int")
+    idx_t = "unsigned long" if ib == 8 else "unsigned int"
+    path = db.lanes[0][0].last_path()
+    names = {2: ["CollectRanges<%d, %s" % (fmt_id, idx_t), "ScanTiles+ScanFinish", "ConvertRanges<%d, %s" % (fmt_id, idx_t)],
+             1: ["", "", "ParseTiles<%d, %s" % (fmt_id, idx_t)],
+             0: ["WalkText<%d, %s, 0" % (fmt_id, idx_t), "ScanTiles+ScanFinish", "WalkText<%d, %s, 1" % (fmt_id, idx_t)]}[path]
+    kernel_name = names[kms.index(dominant_ms)]
     traffic = ncu_traffic(kernel_name)
     roofline = {"bound": "hbm", "kernel": kernel_name + ", ...>", "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -625,6 +629,8 @@ def main():
                 "traffic_source": traffic,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": int(b_alg),
                 "launch_ms": dominant_ms,
+                "kernels_of_the_path": {"path": {0: "two-pass walk", 1: "one launch", 2: "collect / scan / convert"}[path],
+                                        "names": names, "ms": kms},
                 "all_kernels": {"count_ms": kms[0], "scan_ms": kms[1], "parse_or_emit_ms": kms[2],
                                 "achieved": b_alg / (total_ms * 1e-3) / GB,
                                 "frac": b_alg / (total_ms * 1e-3) / GB / peak},

@@ -27,7 +27,7 @@ EXPORTS = (
     "b200p_set_host_threads", "b200p_copied_bytes", "b200p_next_to", "b200p_host_alloc",
     "b200p_host_free",
     "b200p_set_profiling", "b200p_kernel_time", "b200p_version", "b200p_parse_device_noalloc",
-    "b200p_block_max", "b200p_current_device", "b200p_device_count", "b200p_set_delivery",
+    "b200p_block_max", "b200p_current_device", "b200p_device_count", "b200p_set_delivery", "b200p_last_path",
 )
 
 
@@ -113,6 +113,8 @@ def load():
     lib.b200p_set_host_threads.restype = C.c_int
     lib.b200p_copied_bytes.argtypes = [H, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.b200p_copied_bytes.restype = C.c_int
+    lib.b200p_last_path.argtypes = [H]
+    lib.b200p_last_path.restype = C.c_int
     lib.b200p_set_delivery.argtypes = [H, C.c_int]
     lib.b200p_set_delivery.restype = C.c_int
     lib.b200p_current_device.argtypes = []
@@ -287,6 +289,10 @@ class Parser(object):
 
     def launch_count(self):
         return int(self.lib.b200p_launch_count(self.handle))
+
+    def last_path(self):
+        """0 = two-pass walk, 1 = ParseTiles, 2 = CollectRanges / ConvertRanges (chunk finished last)."""
+        return int(self.lib.b200p_last_path(self.handle))
 
     def host_alloc(self, nbytes):
         """Pinned, huge-page backed host memory (address); release with host_free()."""

@@ -28,6 +28,7 @@
 #include "host_pool.h"
 #include "text_kernels.cuh"
 #include "tile_kernels.cuh"
+#include "split_kernels.cuh"
 
 namespace b200p {
 
@@ -69,6 +70,10 @@ struct Slot {
   unsigned char *d_tiles; /* one-launch kernel: ticket + look-back status words */
   uint64_t tiles_cap;     /* in tiles */
   bool ran_tiles;         /* the chunk in flight went through ParseTiles */
+  bool ran_split;         /* ... through CollectRanges / ConvertRanges */
+  unsigned char *d_queues; /* 256-byte header (the give-up word) + the role queues of every range */
+  uint64_t queues_cap;     /* bytes */
+  uint32_t split_range, split_pool, split_rows, split_stride;   /* what the chunk in flight was collected with */
   ChunkSummary *d_summary;
   ChunkSummary *h_summary; /* pinned */
   Arrays dev;
@@ -140,7 +145,8 @@ struct b200p_parser_s {
   /* one-launch kernel (ParseTiles): used while the input suits it; a chunk it gives up on is
      parsed again by the two-pass kernels, and after kTileStrikes such chunks the handle stays
      with the two-pass kernels */
-  std::atomic<bool> use_tiles;
+  std::atomic<bool> use_tiles, use_split;
+  std::atomic<int> last_path;   /* B200P_PATH_* of the chunk finished last */
   std::atomic<int> tile_fallbacks;
   uint32_t sub_bytes, over_bytes;
   std::atomic<uint32_t> pool_div;
@@ -578,6 +584,114 @@ static int EnqueueTiles(b200p_handle h, Slot *s) {
   return B200P_OK;
 }
 
+static int ProvisionArrays(b200p_handle h, Slot *s);
+
+/* ---- collect / convert as two launches (split_kernels.cuh): LibSVM and LibFM ---- */
+static bool SplitSuits(const b200p_handle h) {
+  return h->use_split && h->use_tiles && h->cfg.format != B200P_FORMAT_CSV;
+}
+
+static SplitParams MakeSplitParams(const b200p_handle h, const Slot &s) {
+  SplitParams sp;
+  std::memset(&sp, 0, sizeof(sp));
+  sp.walk = MakeParams(h, s);
+  sp.walk.range_bytes = s.split_range;
+  sp.walk.num_ranges = static_cast<uint32_t>((s.nbytes + s.split_range - 1) / s.split_range);
+  sp.walk.num_tiles = (sp.walk.num_ranges + kScanTile - 1) / kScanTile;
+  sp.walk.tile_base = s.d_counts + static_cast<size_t>(kNumCounters) * sp.walk.num_ranges;
+  sp.queues = reinterpret_cast<uint16_t *>(s.d_queues + 256);
+  sp.queue_stride = s.split_stride;
+  sp.cap_pool = s.split_pool;
+  sp.cap_rows = s.split_rows;
+  sp.give_up = reinterpret_cast<uint32_t *>(s.d_queues);
+  return sp;
+}
+
+template <int FMT, typename IdxT>
+static void LaunchCollect(const SplitParams &sp, cudaStream_t st, bool qids) {
+  const unsigned grid = (sp.walk.num_ranges + kSplitWarps - 1) / kSplitWarps;
+  if (FMT == kLibSVM && qids) {
+    CollectRanges<FMT, IdxT, FMT == kLibSVM><<<grid, kSplitThreads, 0, st>>>(sp);
+  } else {
+    CollectRanges<FMT, IdxT, false><<<grid, kSplitThreads, 0, st>>>(sp);
+  }
+}
+template <int FMT, typename IdxT>
+static void LaunchConvert(const SplitParams &sp, cudaStream_t st) {
+  const unsigned grid = (sp.walk.num_ranges + kSplitWarps - 1) / kSplitWarps;
+  ConvertRanges<FMT, IdxT><<<grid, kSplitThreads, 0, st>>>(sp);
+}
+
+static int EnqueueConvert(b200p_handle h, Slot *s) {
+  const SplitParams sp = MakeSplitParams(h, *s);
+  const bool wide = h->cfg.index_bytes == 8;
+  ProfBegin(h, B200P_KERNEL_EMIT, s->stream);
+  if (h->cfg.format == B200P_FORMAT_LIBSVM) {
+    if (wide) LaunchConvert<kLibSVM, uint64_t>(sp, s->stream); else LaunchConvert<kLibSVM, uint32_t>(sp, s->stream);
+  } else {
+    if (wide) LaunchConvert<kLibFM, uint64_t>(sp, s->stream); else LaunchConvert<kLibFM, uint32_t>(sp, s->stream);
+  }
+  ProfEnd(h, s->stream);
+  ++h->launches;
+  CUDA_TRY(h, cudaGetLastError());
+  CUDA_TRY(h, cudaMemcpyAsync(s->h_summary, s->d_summary, sizeof(ChunkSummary),
+                              cudaMemcpyDeviceToHost, s->stream));
+  return B200P_OK;
+}
+
+static int EnqueueSplit(b200p_handle h, Slot *s) {
+  const bool libfm = h->cfg.format == B200P_FORMAT_LIBFM;
+  const uint32_t range_bytes = std::min<uint32_t>(RangeBytesFor(h, s->nbytes), 32768u);   /* 16-bit positions */
+  const uint64_t ranges = (s->nbytes + range_bytes - 1) / range_bytes;
+  const uint32_t div = h->pool_div;
+  s->split_range = range_bytes;
+  s->split_pool = std::max(256u, range_bytes / div);
+  s->split_rows = std::max(64u, range_bytes / (4u * div));
+  s->split_stride = libfm ? SplitQueueEntries<kLibFM>(s->split_pool, s->split_rows)
+                          : SplitQueueEntries<kLibSVM>(s->split_pool, s->split_rows);
+  if (ranges > s->counts_cap) {
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+    cudaFree(s->d_counts);
+    s->d_counts = NULL;
+    s->counts_cap = 0;
+    const uint64_t cap = ranges + ranges / 4 + 64;
+    CUDA_TRY(h, DeviceAlloc(reinterpret_cast<void **>(&s->d_counts),
+                           (cap + cap / kScanTile + 2) * kNumCounters * sizeof(uint32_t)));
+    s->counts_cap = cap;
+  }
+  const uint64_t need = 256 + ranges * s->split_stride * sizeof(uint16_t);
+  if (need > s->queues_cap) {
+    CUDA_TRY(h, cudaStreamSynchronize(s->stream));
+    cudaFree(s->d_queues);
+    s->d_queues = NULL;
+    s->queues_cap = 0;
+    const uint64_t cap = need + need / 8;
+    CUDA_TRY(h, DeviceAlloc(reinterpret_cast<void **>(&s->d_queues), cap));
+    s->queues_cap = cap;
+  }
+  const int rc = ProvisionArrays(h, s);
+  if (rc != B200P_OK) return rc;
+  const SplitParams sp = MakeSplitParams(h, *s);
+  const bool wide = h->cfg.index_bytes == 8;
+  CUDA_TRY(h, cudaMemsetAsync(s->d_queues, 0, 256, s->stream));
+  ProfBegin(h, B200P_KERNEL_COUNT, s->stream);
+  if (libfm) {
+    if (wide) LaunchCollect<kLibFM, uint64_t>(sp, s->stream, false); else LaunchCollect<kLibFM, uint32_t>(sp, s->stream, false);
+  } else {
+    if (wide) LaunchCollect<kLibSVM, uint64_t>(sp, s->stream, h->saw_qids); else LaunchCollect<kLibSVM, uint32_t>(sp, s->stream, h->saw_qids);
+  }
+  ProfEnd(h, s->stream);
+  ProfBegin(h, B200P_KERNEL_SCAN, s->stream);
+  ScanTiles<<<sp.walk.num_tiles, kScanTile, 0, s->stream>>>(sp.walk.counts, sp.walk.num_ranges, sp.walk.tile_base, sp.walk.num_tiles);
+  ScanFinish<<<1, kScanTile, 0, s->stream>>>(sp.walk.tile_base, sp.walk.num_tiles, sp.walk.num_ranges, s->d_summary, sp.give_up);
+  ProfEnd(h, s->stream);
+  h->launches += 3;
+  CUDA_TRY(h, cudaGetLastError());
+  s->ran_tiles = false;
+  s->ran_split = true;
+  return EnqueueConvert(h, s);
+}
+
 /* pass 2 (+ the CSV label clear), then the summary travels to the host */
 static int EnqueueEmit(b200p_handle h, Slot *s) {
   const WalkParams p = MakeParams(h, *s);
@@ -610,6 +724,7 @@ static int ProvisionArrays(b200p_handle h, Slot *s) {
 /* pass 1 + scan + (speculative) pass 2 for the chunk described by s->text / s->nbytes */
 static int EnqueueTwoPass(b200p_handle h, Slot *s) {
   s->ran_tiles = false;
+  s->ran_split = false;
   const uint32_t range_bytes = RangeBytesFor(h, s->nbytes);
   const uint64_t ranges = (s->nbytes + range_bytes - 1) / range_bytes;
   if (ranges > s->counts_cap) {
@@ -631,7 +746,7 @@ static int EnqueueTwoPass(b200p_handle h, Slot *s) {
   ProfEnd(h, s->stream);
   ProfBegin(h, B200P_KERNEL_SCAN, s->stream);
   ScanTiles<<<p.num_tiles, kScanTile, 0, s->stream>>>(p.counts, p.num_ranges, p.tile_base, p.num_tiles);
-  ScanFinish<<<1, kScanTile, 0, s->stream>>>(p.tile_base, p.num_tiles, p.num_ranges, s->d_summary);
+  ScanFinish<<<1, kScanTile, 0, s->stream>>>(p.tile_base, p.num_tiles, p.num_ranges, s->d_summary, NULL);
   ProfEnd(h, s->stream);
   h->launches += 3;
   CUDA_TRY(h, cudaGetLastError());
@@ -645,12 +760,14 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
     std::memset(s->h_summary, 0, sizeof(ChunkSummary));
     return B200P_OK;
   }
+  if (SplitSuits(h)) return EnqueueSplit(h, s);
   if (!TilesSuit(h)) return EnqueueTwoPass(h, s);
   const uint64_t tile_bytes = static_cast<uint64_t>(kTileWarps) * h->sub_bytes;
   const uint64_t tiles = (s->nbytes + tile_bytes - 1) / tile_bytes;
   if (tiles > s->tiles_cap) {
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
     cudaFree(s->d_tiles);
+  cudaFree(s->d_queues);
     s->d_tiles = NULL;
     s->tiles_cap = 0;
     const uint64_t cap = tiles + tiles / 4 + 16;
@@ -660,6 +777,7 @@ static int EnqueueParse(b200p_handle h, Slot *s) {
   const int rc = ProvisionArrays(h, s);
   if (rc != B200P_OK) return rc;
   s->ran_tiles = true;
+  s->ran_split = false;
   return EnqueueTiles(h, s);
 }
 
@@ -669,7 +787,7 @@ static int FinishParse(b200p_handle h, Slot *s) {
   if (s->nbytes == 0) return B200P_OK;
   CUDA_TRY(h, cudaStreamSynchronize(s->stream));
   const ChunkSummary &sum = *s->h_summary;
-  if (s->ran_tiles && (sum.error & kErrFallback) != 0u && (sum.error & kErrInternal) == 0u) {
+  if ((s->ran_tiles || s->ran_split) && (sum.error & kErrFallback) != 0u && (sum.error & kErrInternal) == 0u) {
     /* the one-launch kernel met something it does not take (a line longer than its overhang,
        text denser than its queues): this chunk goes through the two-pass kernels, and a handle
        that keeps meeting such chunks stops trying */
@@ -685,10 +803,11 @@ static int FinishParse(b200p_handle h, Slot *s) {
   if (sum.total[kRows] > s->dev.cap_rows || sum.total[kNnz] > s->dev.cap_nnz) {
     const int rc = EnsureArrays(h, &s->dev, sum.total[kRows], sum.total[kNnz], false);
     if (rc != B200P_OK) return rc;
-    const int rc2 = s->ran_tiles ? EnqueueTiles(h, s) : EnqueueEmit(h, s);
+    const int rc2 = s->ran_tiles ? EnqueueTiles(h, s) : (s->ran_split ? EnqueueConvert(h, s) : EnqueueEmit(h, s));
     if (rc2 != B200P_OK) return rc2;
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
   }
+  h->last_path = s->ran_tiles ? B200P_PATH_ONE_LAUNCH : (s->ran_split ? B200P_PATH_COLLECT_CONVERT : B200P_PATH_TWO_PASS);
   if (sum.total[kQids] != 0) h->saw_qids = true;
   {
     std::lock_guard<std::mutex> g(h->mu);
@@ -739,6 +858,7 @@ static void DestroySlot(Slot *s) {
   cudaFree(s->d_text);
   cudaFree(s->d_counts);
   cudaFree(s->d_tiles);
+  cudaFree(s->d_queues);
   cudaFree(s->d_summary);
   cudaFreeHost(s->h_summary);
   FreeDeviceArrays(&s->dev);
@@ -881,7 +1001,10 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
        B200P_SUB_BYTES / B200P_OVER_BYTES are tuning knobs of the one-launch kernel */
     const char *off = std::getenv("B200P_TILES");
     h->use_tiles = !(off != NULL && off[0] == '0');
+    const char *off2 = std::getenv("B200P_SPLIT");    /* B200P_SPLIT=0: LibSVM / LibFM through ParseTiles as well */
+    h->use_split = !(off2 != NULL && off2[0] == '0');
     h->tile_fallbacks = 0;
+    h->last_path = -1;
     uint32_t sub = 2048u, over = 4096u;
     const char *e1 = std::getenv("B200P_SUB_BYTES"), *e2 = std::getenv("B200P_OVER_BYTES");
     if (e1 != NULL && std::atoi(e1) > 0) sub = static_cast<uint32_t>(std::atoi(e1));
@@ -958,6 +1081,8 @@ void b200p_destroy(b200p_handle h) {
 }
 
 uint64_t b200p_launch_count(b200p_handle h) { return h != NULL ? h->launches.load() : 0; }
+
+int b200p_last_path(b200p_handle h) { return h != NULL ? h->last_path.load() : -1; }
 
 int b200p_set_profiling(b200p_handle h, int on) {
   if (h == NULL) return B200P_E_INVALID;
@@ -1649,7 +1774,7 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *rq, b200p_rowblock *
   NOALLOC_TRY(cudaMemsetAsync(&scratch->summary, 0, sizeof(ChunkSummary), stream));
   LaunchWalkPlain(rq->format, wide, p, stream, false);
   ScanTiles<<<p.num_tiles, kScanTile, 0, stream>>>(p.counts, p.num_ranges, p.tile_base, p.num_tiles);
-  ScanFinish<<<1, kScanTile, 0, stream>>>(p.tile_base, p.num_tiles, p.num_ranges, &scratch->summary);
+  ScanFinish<<<1, kScanTile, 0, stream>>>(p.tile_base, p.num_tiles, p.num_ranges, &scratch->summary, NULL);
   if (rq->format == B200P_FORMAT_CSV) {
     ZeroLabels<<<296, 256, 0, stream>>>(p.label, &scratch->summary, p.cap_rows, p.cap_nnz);
   }

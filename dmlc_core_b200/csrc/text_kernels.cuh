@@ -1080,7 +1080,8 @@ __global__ void __launch_bounds__(kScanTile) ScanTiles(uint32_t *counts, uint32_
 }
 
 __global__ void __launch_bounds__(kScanTile) ScanFinish(uint32_t *tile_base, uint32_t num_tiles,
-                                                        uint32_t num_ranges, ChunkSummary *summary) {
+                                                        uint32_t num_ranges, ChunkSummary *summary,
+                                                        const uint32_t *extra_error) {
   __shared__ uint32_t warp_sums[32];
   __shared__ uint32_t total;
   __shared__ unsigned long long grand[kNumCounters];
@@ -1102,6 +1103,7 @@ __global__ void __launch_bounds__(kScanTile) ScanFinish(uint32_t *tile_base, uin
 #pragma unroll
     for (int c = 0; c < kNumCounters; ++c) summary->total[c] = grand[c];
     if (grand[kValues] != 0ull && grand[kValues] != grand[kNnz]) err |= kErrValueCount;
+    if (extra_error != NULL) err |= *extra_error;   /* bits the collecting kernel of split_kernels.cuh raised */
     summary->error = err;
     summary->ranges = num_ranges;
   }

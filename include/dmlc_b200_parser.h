@@ -232,6 +232,20 @@ int b200p_fetch(b200p_handle h, void *host_dst, const void *device_src, uint64_t
 uint64_t b200p_launch_count(b200p_handle h);
 
 /*
+ * Which kernels parsed the chunk finished last on this handle (-1 before the first):
+ *   B200P_PATH_COLLECT_CONVERT  CollectRanges, ScanTiles, ScanFinish, ConvertRanges: LibSVM and LibFM
+ *   B200P_PATH_ONE_LAUNCH       ParseTiles: CSV with the label in column 0 or no label column
+ *   B200P_PATH_TWO_PASS         WalkText (count), the scan, WalkText (emit): CSV with a later label
+ *                               column, and every chunk the other two hand over (a line longer than
+ *                               their windows, text denser than their queues)
+ * All three produce the same arrays. No reference counterpart.
+ */
+#define B200P_PATH_TWO_PASS 0
+#define B200P_PATH_ONE_LAUNCH 1
+#define B200P_PATH_COLLECT_CONVERT 2
+int b200p_last_path(b200p_handle h);
+
+/*
  * Allocation-free variant of b200p_parse_device. It has no counterpart in the reference.
  *
  * For callers that cannot allocate GPU memory while they run: the card was handed over in full
@@ -282,9 +296,9 @@ int b200p_parse_device_noalloc(const b200p_noalloc_request *request, b200p_rowbl
  * switched on. No reference counterpart (the reference only prints wall-clock MB/s,
  * test/libsvm_parser_test.cc:27-31).
  */
-#define B200P_KERNEL_COUNT 0 /* pass 1: WalkText<EMIT=false> */
-#define B200P_KERNEL_SCAN 1  /* ScanRanges */
-#define B200P_KERNEL_EMIT 2  /* pass 2: WalkText<EMIT=true> */
+#define B200P_KERNEL_COUNT 0 /* CollectRanges, or pass 1 of the walk (WalkText<EMIT=false>) */
+#define B200P_KERNEL_SCAN 1  /* ScanTiles + ScanFinish */
+#define B200P_KERNEL_EMIT 2  /* ConvertRanges, ParseTiles, or pass 2 of the walk (WalkText<EMIT=true>) */
 int b200p_set_profiling(b200p_handle h, int on);
 int b200p_kernel_time(b200p_handle h, int kernel, double *total_ms, uint64_t *launches);
 

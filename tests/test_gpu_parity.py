@@ -14,11 +14,14 @@ from oracle.pyoracle import same_rowblocks
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["tiles", "two-pass"])
+@pytest.fixture(params=["default", "tiles", "two-pass"])
 def kernel_path(request, monkeypatch):
-    """Both kernel paths behind the same entry points: the one-launch ParseTiles kernel (default)
-    and the count / scan / emit walk it falls back to (B200P_TILES=0 is read by b200p_create)."""
-    monkeypatch.setenv("B200P_TILES", "1" if request.param == "tiles" else "0")
+    """The kernel paths behind the same entry points (the switches are read by b200p_create):
+    default   collect / scan / convert for LibSVM and LibFM, the one-launch ParseTiles kernel for CSV
+    tiles     ParseTiles for every format (B200P_SPLIT=0)
+    two-pass  the count / scan / emit walk the others fall back to (B200P_TILES=0)"""
+    monkeypatch.setenv("B200P_TILES", "0" if request.param == "two-pass" else "1")
+    monkeypatch.setenv("B200P_SPLIT", "0" if request.param == "tiles" else "1")
     return request.param
 
 
@@ -500,13 +503,16 @@ def test_next_to_lands_blocks_in_caller_memory(cuda_lib, oracle, kind, fmt, ib, 
     assert same_rowblocks(got, exp) is None
 
 
-def test_one_launch_kernel_hands_over_what_it_does_not_take(cuda_lib, oracle):
-    """ParseTiles gives up on a chunk with a line longer than its staged overhang, or with text
-    denser than its token queues; the chunk is then parsed by the two-pass kernels.  Dense text
-    makes the handle switch to larger queues once; after two other such chunks it stays with the
-    two-pass kernels.  Results are the oracle's either way; the launch count shows which kernels
-    ran (one launch per chunk for ParseTiles, four more for the walk)."""
+@pytest.mark.parametrize("split", [True, False])
+def test_kernels_hand_over_what_they_do_not_take(cuda_lib, oracle, monkeypatch, split):
+    """CollectRanges (default for LibSVM / LibFM) and ParseTiles give up on a chunk with a line too
+    long for them or with text denser than their token queues; the chunk is then parsed by the
+    two-pass kernels.  Dense text makes the handle switch to larger queues once; after two other
+    such chunks it stays with the two-pass kernels.  Results are the oracle's either way; the
+    launch count shows which kernels ran."""
     from gpu_util import parse_on_device
+    monkeypatch.setenv("B200P_SPLIT", "1" if split else "0")
+    own = 4 if split else 1                    # collect, scan x 2, convert / ParseTiles
     plain = (b"1 " + b" ".join(b"%d:%d.5" % (100000 + i, i) for i in range(1, 40)) + b"\n") * 400
     long_line = b"1 " + b" ".join(b"%d:%d.25" % (i, i) for i in range(1, 9000)) + b"\n" + plain
     dense = (b"1 " + b" ".join(b"%d:1" % (i % 90) for i in range(40)) + b"\n") * 600      # ~2.5 bytes per token
@@ -519,10 +525,10 @@ def test_one_launch_kernel_hands_over_what_it_does_not_take(cuda_lib, oracle):
         counts.append(p.launch_count() - before)
         assert same_rowblocks(got, oracle.parse_buffer("libsvm", text, 4, -1)) is None
     p.close()
-    assert counts[0] == 1                          # ParseTiles alone
-    assert counts[1] >= 5 and counts[2] == 1       # dense: handed over once, then larger queues
-    assert counts[3] >= 5 and counts[4] == 1       # a long line: handed over (first strike)
-    assert counts[5] >= 5 and counts[6] >= 4       # second strike: the handle stays on the walk
+    assert counts[0] == own
+    assert counts[1] >= own + 4 and counts[2] == own       # dense: handed over once, then larger queues
+    assert counts[3] >= own + 4 and counts[4] == own       # a long line: handed over (first strike)
+    assert counts[5] >= own + 4 and counts[6] >= 4         # second strike: the handle stays on the walk
     # CSV rows longer than a tile are not a problem (fields, not lines, are what a warp owns)
     wide = (b",".join(b"%d.5" % i for i in range(20000)) + b"\n") * 3
     p = _parser(cuda_lib, "csv", 4, 0)
