@@ -146,6 +146,7 @@ struct b200p_parser_s {
      parsed again by the two-pass kernels, and after kTileStrikes such chunks the handle stays
      with the two-pass kernels */
   std::atomic<bool> use_tiles, use_split;
+  bool split_csv;
   std::atomic<int> last_path;   /* B200P_PATH_* of the chunk finished last */
   std::atomic<int> tile_fallbacks;
   uint32_t sub_bytes, over_bytes;
@@ -588,7 +589,11 @@ static int ProvisionArrays(b200p_handle h, Slot *s);
 
 /* ---- collect / convert as two launches (split_kernels.cuh): LibSVM and LibFM ---- */
 static bool SplitSuits(const b200p_handle h) {
-  return h->use_split && h->use_tiles && h->cfg.format != B200P_FORMAT_CSV;
+  if (!h->use_split || !h->use_tiles) return false;
+  /* CSV with the label in a later column needs a column id per field: two-pass kernels.
+     B200P_SPLIT_CSV=0 keeps CSV on the one-launch kernel. */
+  if (h->cfg.format == B200P_FORMAT_CSV) return h->split_csv && h->cfg.label_column <= 0;
+  return true;
 }
 
 static SplitParams MakeSplitParams(const b200p_handle h, const Slot &s) {
@@ -626,7 +631,11 @@ static int EnqueueConvert(b200p_handle h, Slot *s) {
   const SplitParams sp = MakeSplitParams(h, *s);
   const bool wide = h->cfg.index_bytes == 8;
   ProfBegin(h, B200P_KERNEL_EMIT, s->stream);
-  if (h->cfg.format == B200P_FORMAT_LIBSVM) {
+  if (h->cfg.format == B200P_FORMAT_CSV) {
+    const unsigned grid = (sp.walk.num_ranges + kSplitWarps - 1) / kSplitWarps;
+    if (wide) ConvertFieldRanges<uint64_t><<<grid, kSplitThreads, 0, s->stream>>>(sp);
+    else ConvertFieldRanges<uint32_t><<<grid, kSplitThreads, 0, s->stream>>>(sp);
+  } else if (h->cfg.format == B200P_FORMAT_LIBSVM) {
     if (wide) LaunchConvert<kLibSVM, uint64_t>(sp, s->stream); else LaunchConvert<kLibSVM, uint32_t>(sp, s->stream);
   } else {
     if (wide) LaunchConvert<kLibFM, uint64_t>(sp, s->stream); else LaunchConvert<kLibFM, uint32_t>(sp, s->stream);
@@ -640,15 +649,21 @@ static int EnqueueConvert(b200p_handle h, Slot *s) {
 }
 
 static int EnqueueSplit(b200p_handle h, Slot *s) {
-  const bool libfm = h->cfg.format == B200P_FORMAT_LIBFM;
+  const bool libfm = h->cfg.format == B200P_FORMAT_LIBFM, csv = h->cfg.format == B200P_FORMAT_CSV;
   const uint32_t range_bytes = std::min<uint32_t>(RangeBytesFor(h, s->nbytes), 32768u);   /* 16-bit positions */
   const uint64_t ranges = (s->nbytes + range_bytes - 1) / range_bytes;
   const uint32_t div = h->pool_div;
   s->split_range = range_bytes;
-  s->split_pool = std::max(256u, range_bytes / div);
-  s->split_rows = std::max(64u, range_bytes / (4u * div));
-  s->split_stride = libfm ? SplitQueueEntries<kLibFM>(s->split_pool, s->split_rows)
-                          : SplitQueueEntries<kLibSVM>(s->split_pool, s->split_rows);
+  if (csv) {
+    s->split_pool = range_bytes / 2u;                              /* a range cannot start more fields */
+    s->split_rows = std::max(64u, range_bytes / (2u * div));       /* rows of 8 (4 once dense) bytes and more */
+    s->split_stride = SplitCsvEntries(s->split_pool, s->split_rows);
+  } else {
+    s->split_pool = std::max(256u, range_bytes / div);
+    s->split_rows = std::max(64u, range_bytes / (4u * div));
+    s->split_stride = libfm ? SplitQueueEntries<kLibFM>(s->split_pool, s->split_rows)
+                            : SplitQueueEntries<kLibSVM>(s->split_pool, s->split_rows);
+  }
   if (ranges > s->counts_cap) {
     CUDA_TRY(h, cudaStreamSynchronize(s->stream));
     cudaFree(s->d_counts);
@@ -675,7 +690,11 @@ static int EnqueueSplit(b200p_handle h, Slot *s) {
   const bool wide = h->cfg.index_bytes == 8;
   CUDA_TRY(h, cudaMemsetAsync(s->d_queues, 0, 256, s->stream));
   ProfBegin(h, B200P_KERNEL_COUNT, s->stream);
-  if (libfm) {
+  if (csv) {
+    const unsigned grid = (sp.walk.num_ranges + kSplitWarps - 1) / kSplitWarps;
+    if (wide) CollectFieldRanges<uint64_t><<<grid, kSplitThreads, 0, s->stream>>>(sp);
+    else CollectFieldRanges<uint32_t><<<grid, kSplitThreads, 0, s->stream>>>(sp);
+  } else if (libfm) {
     if (wide) LaunchCollect<kLibFM, uint64_t>(sp, s->stream, false); else LaunchCollect<kLibFM, uint32_t>(sp, s->stream, false);
   } else {
     if (wide) LaunchCollect<kLibSVM, uint64_t>(sp, s->stream, h->saw_qids); else LaunchCollect<kLibSVM, uint32_t>(sp, s->stream, h->saw_qids);
@@ -1003,6 +1022,8 @@ int b200p_create(const b200p_config *config, b200p_handle *out) {
     h->use_tiles = !(off != NULL && off[0] == '0');
     const char *off2 = std::getenv("B200P_SPLIT");    /* B200P_SPLIT=0: LibSVM / LibFM through ParseTiles as well */
     h->use_split = !(off2 != NULL && off2[0] == '0');
+    const char *off3 = std::getenv("B200P_SPLIT_CSV");
+    h->split_csv = !(off3 != NULL && off3[0] == '0');
     h->tile_fallbacks = 0;
     h->last_path = -1;
     uint32_t sub = 2048u, over = 4096u;

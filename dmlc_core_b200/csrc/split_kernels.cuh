@@ -20,9 +20,9 @@
  * The queues cost DRAM traffic (2 bytes per token each way, about half the text size together)
  * on a path that sits far below the HBM roofline because it is bound by instruction issue; they
  * buy a front-end that runs once and two kernels without a single barrier.
- * LibSVM and LibFM only (CSV keeps the one-launch kernel: its pass 1 was a popcount anyway).
- * A range whose lines span more than 64 KiB, or hold more tokens or rows than its queues, raises
- * kErrFallback and the chunk goes through the two-pass kernels.
+ * A range whose lines span more than 64 KiB (LibSVM / LibFM), or which holds more tokens or rows
+ * than its queues, raises kErrFallback and the chunk goes through the two-pass kernels; so does
+ * CSV with the label in a later column than the first (it needs a column id per field).
  */
 #ifndef DMLC_CORE_B200_SPLIT_KERNELS_CUH_
 #define DMLC_CORE_B200_SPLIT_KERNELS_CUH_
@@ -324,24 +324,18 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams
     asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
     asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 20));
   };
-  uint32_t p_index = 0, p_field = 0, p_value = 0;
-  if (lane < n[kNnz]) {
-    p_index = q16[lane];
-    if constexpr (FMT == kLibFM) p_field = q16[at.field + lane];
-  }
-  if (lane < n[kValues]) p_value = q16[sp.cap_pool - 1u - lane];
+  /* pipeline: positions of trip t+1 (a*) and t+2 (b*) are in registers, those of t+3 are being
+     read; the text of trip t+2 is requested while trip t is converted */
+  const auto index_at = [&](uint32_t k) -> uint32_t { return k < n[kNnz] ? q16[k] : 0u; };
+  const auto field_at = [&](uint32_t k) -> uint32_t { return (FMT == kLibFM && k < n[kNnz]) ? q16[at.field + k] : 0u; };
+  const auto value_at = [&](uint32_t k) -> uint32_t { return k < n[kValues] ? q16[sp.cap_pool - 1u - k] : 0u; };
+  uint32_t p_index = index_at(lane), p_field = field_at(lane), p_value = value_at(lane);
+  uint32_t a_index = index_at(lane + 32u), a_field = field_at(lane + 32u), a_value = value_at(lane + 32u);
+  uint32_t b_index = index_at(lane + 64u), b_field = field_at(lane + 64u), b_value = value_at(lane + 64u);
   for (uint32_t i = lane; i < sweep; i += 32u) {
-    uint32_t nx_index = 0, nx_field = 0, nx_value = 0;
-    const uint32_t j = i + 32u;
-    if (j < n[kNnz]) {
-      nx_index = q16[j];
-      if constexpr (FMT == kLibFM) nx_field = q16[at.field + j];
-      prefetch(FMT == kLibFM ? nx_field : nx_index);
-    }
-    if (j < n[kValues]) {
-      nx_value = q16[sp.cap_pool - 1u - j];
-      prefetch(nx_value);
-    }
+    const uint32_t c_index = index_at(i + 96u), c_field = field_at(i + 96u), c_value = value_at(i + 96u);
+    if (i + 64u < n[kNnz]) prefetch(FMT == kLibFM ? b_field : b_index);
+    if (i + 64u < n[kValues]) prefetch(b_value);
     if (i < n[kNnz]) {
       if constexpr (FMT == kLibFM) {
         reinterpret_cast<IdxT *>(prm.field)[b[kNnz] + i] =
@@ -350,11 +344,200 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams
       index[b[kNnz] + i] = static_cast<IdxT>(ToUintFast<sizeof(IdxT) == 8>(txt, lo + p_index, &neg));
     }
     if (i < n[kValues]) prm.value[b[kValues] + i] = ToFloatFast(txt, lo + p_value);
-    p_index = nx_index;
-    p_field = nx_field;
-    p_value = nx_value;
+    p_index = a_index; p_field = a_field; p_value = a_value;
+    a_index = b_index; a_field = b_field; a_value = b_value;
+    b_index = c_index; b_field = c_field; b_value = c_value;
   }
   if (__any_sync(0xffffffffu, neg) && lane == 0) atomicOr(&prm.summary->error, static_cast<unsigned int>(kErrNegativeIndex));
+}
+
+/* ---------------------------------------------------------------- CSV ------------------------- */
+/*
+ * CSV (label in column 0, or no label column): rows need no pairing, so a warp owns the FIELDS
+ * that start in its range, whatever row they belong to (reference csv_parser.h:73-102: every
+ * field is a float; column label_column is the label, every other column an (index, value)
+ * entry whose index is its position among the row's value columns).  A range block holds the
+ * value positions, the first field of every row that starts in the range, the number of values
+ * in front of each of those rows, and -- for the column ids of values that continue a row begun
+ * in an earlier range -- how many values follow the range's last row start.
+ */
+__host__ __device__ inline uint32_t SplitCsvEntries(uint32_t cap_pool, uint32_t cap_rows) {
+  return (cap_pool + 2u * cap_rows + 2u + 7u) & ~7u;    /* values, row_at, row_nnz, 2 entries of meta */
+}
+
+template <typename IdxT>
+__global__ void __launch_bounds__(kSplitThreads) CollectFieldRanges(const SplitParams sp) {
+  __shared__ __align__(16) uint8_t lut[256];
+  const WalkParams &prm = sp.walk;
+  for (int c = threadIdx.x; c < 256; c += kSplitThreads) lut[c] = static_cast<uint8_t>(ClassEntry<kCSV>(c));
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const uint32_t range = blockIdx.x * kSplitWarps + (threadIdx.x >> 5);
+  if (range >= prm.num_ranges) return;
+  uint16_t *const q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  const uint32_t o_row_at = sp.cap_pool, o_row_nnz = sp.cap_pool + sp.cap_rows, o_meta = sp.cap_pool + 2u * sp.cap_rows;
+  const uint32_t lo = range * prm.range_bytes;
+  const uint32_t hi = min(lo + prm.range_bytes, prm.size);
+  const bool labelled = prm.label_column == 0;
+  uint32_t n_rows = 0, n_value = 0, last_row_nnz = 0;
+  bool has_row = false, give_up = false;
+  /* class of the byte in front of the range (separator | EOL << 1); the chunk starts a line */
+  uint32_t carry = lo == 0u ? 3u : lut[__ldg(prm.text + lo - 1u)];
+  const uint8_t *const my_text = prm.text + 16u * lane;
+  const auto whole = [&](uint32_t b) { return b + kStepBytes <= hi; };   /* hi <= size: the loads stay inside the chunk */
+  uint4 ahead = make_uint4(0u, 0u, 0u, 0u);
+  if (whole(lo)) ahead = __ldg(reinterpret_cast<const uint4 *>(my_text + lo));
+  for (uint32_t base = lo; base < hi; base += kStepBytes) {
+    const uint32_t first_byte = base + 16u * lane;
+    uint4 now = ahead;
+    if (!whole(base)) now = Load16(prm.text, prm.size, first_byte);
+    if (whole(base + kStepBytes)) ahead = __ldg(reinterpret_cast<const uint4 *>(my_text + base + kStepBytes));
+    const uint32_t cls = ClassifyLut(now, lut, prm.four);
+    uint32_t keep = kEven;
+    if (!whole(base)) keep = Spread16(KeepMask(first_byte, lo, hi));
+    uint32_t up = __shfl_up_sync(0xffffffffu, cls >> 30, 1);
+    if (lane == 0) up = carry;
+    carry = __shfl_sync(0xffffffffu, cls >> 30, 31);
+    /* a field starts after a comma or at a line start, unless that byte is an EOL
+       (a trailing comma yields no extra column, csv_parser.h:79-95) */
+    const uint32_t before = (cls << 2) | up;
+    const uint32_t not_eol = ~(cls >> 1) & keep;
+    const uint32_t starts = before & not_eol;
+    const uint32_t row_starts = (before >> 1) & not_eol;
+    const uint32_t values = labelled ? (starts & ~row_starts) : starts;
+    const uint32_t nv = __popc(values), nr = __popc(row_starts);
+    /* one scan for both counts: values below, rows above bit 16 (a step holds <= 512 of either) */
+    const uint32_t both = WarpInclusiveSum(nv | (nr << 16), lane);
+    const uint32_t step_both = __shfl_sync(0xffffffffu, both, 31);
+    const uint32_t step_values = step_both & 0xffffu, step_rows = step_both >> 16;
+    if (n_rows + step_rows > sp.cap_rows) {    /* cap_pool = range / 2 always holds the fields */
+      give_up = true;
+      break;
+    }
+    const uint32_t vbase = n_value + (both & 0xffffu) - nv;
+    const uint32_t rel2 = 2u * (first_byte - lo);
+    uint32_t vslot = vbase;
+    uint32_t bits = values;
+    while (bits != 0u) {
+      const uint32_t b = __ffs(bits) - 1;          /* 2 * byte offset */
+      bits &= bits - 1u;
+      q16[vslot] = static_cast<uint16_t>((rel2 + b) >> 1);
+      ++vslot;
+    }
+    if (step_rows != 0u) {
+      uint32_t rslot = n_rows + (both >> 16) - nr;
+      bits = row_starts;
+      while (bits != 0u) {
+        const uint32_t b = __ffs(bits) - 1;
+        bits &= bits - 1u;
+        q16[o_row_at + rslot] = static_cast<uint16_t>((rel2 + b) >> 1);
+        q16[o_row_nnz + rslot] = static_cast<uint16_t>(vbase + __popc(values & ((1u << b) - 1u)));
+        ++rslot;
+      }
+      const uint32_t who = __ballot_sync(0xffffffffu, nr != 0u);
+      const int src = 31 - __clz(who);
+      const uint32_t top = 31u - __clz(row_starts | 1u);
+      last_row_nnz = __shfl_sync(0xffffffffu, vbase + __popc(values & ((1u << top) - 1u)), src);
+      has_row = true;
+    }
+    n_value += step_values;
+    n_rows += step_rows;
+  }
+  if (give_up) {
+    n_rows = n_value = 0u;
+    if (lane == 0) atomicOr(sp.give_up, static_cast<uint32_t>(kErrFallback | kErrDense));
+  }
+  if (lane == 0) {
+    /* values behind the range's last row start (all of them when no row starts here) */
+    const uint32_t tail = has_row ? n_value - last_row_nnz : n_value;
+    q16[o_meta] = static_cast<uint16_t>(tail);
+    q16[o_meta + 1u] = has_row ? 1u : 0u;
+  }
+  if (lane < kNumCounters) {
+    const uint32_t v = lane == kRows ? n_rows : ((lane == kNnz || lane == kValues) ? n_value : 0u);
+    prm.counts[lane * prm.num_ranges + range] = v;
+  }
+}
+
+template <typename IdxT>
+__global__ void __launch_bounds__(kSplitThreads) ConvertFieldRanges(const SplitParams sp) {
+  const WalkParams &prm = sp.walk;
+  const int lane = threadIdx.x & 31;
+  const uint32_t range = blockIdx.x * kSplitWarps + (threadIdx.x >> 5);
+  if (range >= prm.num_ranges) return;
+  const ChunkSummary *sum = prm.summary;
+  if ((sum->error & kErrFallback) != 0u) return;
+  if (sum->total[kRows] > prm.cap_rows || sum->total[kNnz] > prm.cap_nnz) return;
+  if (range == 0 && lane == 0) prm.offset[sum->total[kRows]] = sum->total[kNnz];
+
+  const auto start_of = [&](int c, uint32_t r) -> unsigned long long {
+    return r < prm.num_ranges
+               ? static_cast<unsigned long long>(prm.counts[c * prm.num_ranges + r]) +
+                     prm.tile_base[c * prm.num_tiles + r / kScanTile]
+               : sum->total[c];
+  };
+  const uint32_t b_rows = static_cast<uint32_t>(start_of(kRows, range));
+  const uint32_t b_nnz = static_cast<uint32_t>(start_of(kNnz, range));
+  const uint32_t n_rows = static_cast<uint32_t>(start_of(kRows, range + 1u)) - b_rows;
+  const uint32_t n_value = static_cast<uint32_t>(start_of(kNnz, range + 1u)) - b_nnz;
+  const Text txt = {prm.text, prm.size};
+  const uint32_t lo = range * prm.range_bytes;
+  const uint16_t *const q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  const uint32_t o_row_at = sp.cap_pool, o_row_nnz = sp.cap_pool + sp.cap_rows, o_meta = sp.cap_pool + 2u * sp.cap_rows;
+  const bool labelled = prm.label_column == 0;
+  IdxT *const index = reinterpret_cast<IdxT *>(prm.index);
+
+  /* values: queue entries one trip ahead, their text requested from L2 meanwhile */
+  const uint8_t *const text_lo = prm.text + lo;
+  const auto value_at = [&](uint32_t k) -> uint32_t { return k < n_value ? q16[k] : 0u; };
+  uint32_t p_value = value_at(lane), a_value = value_at(lane + 32u), b_value = value_at(lane + 64u);
+  for (uint32_t i = lane; i < n_value; i += 32u) {
+    const uint32_t c_value = value_at(i + 96u);
+    if (i + 64u < n_value) {
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(text_lo + b_value));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(text_lo + b_value + 20));
+    }
+    prm.value[b_nnz + i] = ToFloatFast(txt, lo + p_value);
+    p_value = a_value;
+    a_value = b_value;
+    b_value = c_value;
+  }
+  for (uint32_t i = lane; i < n_rows; i += 32u) {
+    prm.label[b_rows + i] = labelled ? ToFloatFast(txt, lo + q16[o_row_at + i]) : 0.0f;
+    prm.offset[b_rows + i] = static_cast<unsigned long long>(b_nnz + q16[o_row_nnz + i]);
+  }
+  /* column ids: the j-th value of a row has id j (csv_parser.h:84-88).  The values in front of
+     the range's first row start continue the row that was open when the range began: their ids go
+     on from the values that row holds in the ranges in front (walk back to the nearest range
+     with a row start). */
+  const uint32_t head_len = n_rows != 0u ? q16[o_row_nnz] : n_value;
+  if (head_len != 0u) {
+    uint32_t open = 0;
+    for (uint32_t r = range; r != 0u;) {
+      --r;
+      const uint16_t *m = sp.queues + static_cast<size_t>(r) * sp.queue_stride + o_meta;
+      open += m[0];
+      if (m[1] != 0u) break;
+    }
+    for (uint32_t j = lane; j < head_len; j += 32u) index[b_nnz + j] = static_cast<IdxT>(open + j);
+  }
+  if (n_value >= 16u * n_rows) {
+    for (uint32_t r = 0; r < n_rows; ++r) {
+      const uint32_t s = q16[o_row_nnz + r];
+      const uint32_t e = r + 1u < n_rows ? q16[o_row_nnz + r + 1u] : n_value;
+      for (uint32_t j = s + lane; j < e; j += 32u) index[b_nnz + j] = static_cast<IdxT>(j - s);
+    }
+  } else {
+    /* short rows: every value finds its row by bisection over the row starts */
+    for (uint32_t i = head_len + lane; i < n_value; i += 32u) {
+      uint32_t a = 0, b = n_rows;     /* rows [0, a) start at or before value i */
+      while (a < b) {
+        const uint32_t m = (a + b) >> 1;
+        if (q16[o_row_nnz + m] <= i) a = m + 1u; else b = m;
+      }
+      index[b_nnz + i] = static_cast<IdxT>(i - q16[o_row_nnz + a - 1u]);
+    }
+  }
 }
 
 }  // namespace b200p

@@ -1,8 +1,9 @@
 #!/usr/bin/env python
 """Turn an ncu report brought back in gpurun_out/ into the small tracked summaries under
-profiles/:   python profiles/summarize_ncu.py gpurun_out/<name>.ncu-rep profiles/<out-stem>
-writes <out-stem>.metrics.json (per-kernel headline metrics incl. DRAM bytes per launch) and
-<out-stem>.opcodes.txt (dynamic SASS opcode mix, ALU-pipe vs FMA-pipe share)."""
+profiles/:   python profiles/summarize_ncu.py gpurun_out/<name>.ncu-rep profiles/<out-stem> [text_bytes]
+writes <out-stem>.metrics.json (per-kernel headline metrics incl. DRAM bytes per launch; text_bytes,
+if given, records the size of the chunk the launches parsed so that bench.py can scale the traffic
+to its own window) and <out-stem>.opcodes.txt (dynamic SASS opcode mix, ALU-pipe vs FMA-pipe share)."""
 import collections
 import csv
 import io
@@ -43,11 +44,14 @@ def unit_scale(unit):
 
 def main():
     rep, stem = sys.argv[1], sys.argv[2]
+    text_bytes = int(sys.argv[3]) if len(sys.argv) > 3 else None
     rows = list(csv.reader(io.StringIO(ncu(["-i", rep, "--page", "raw", "--csv"]))))
     hdr, units, data = rows[0], rows[1], rows[2:]
     out = []
     for r in data:
-        k = {"kernel": r[hdr.index("Kernel Name")]}
+        k = {"kernel": r[hdr.index("Kernel Name")], "capture": stem.split("/")[-1]}
+        if text_bytes is not None:
+            k["text_bytes"] = text_bytes
         for m in WANT:
             if m in hdr:
                 i = hdr.index(m)

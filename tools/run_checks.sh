@@ -1,4 +1,3 @@
-# GPU box: the new tests, the probe of the host read path, and a first bench line
-timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_cpp_parser.py tests/test_zz_no_alloc.py -x -q -m gpu -k "hands_over or tile_boundaries or device_csr_out or consumer_is_busy or rewind or noalloc" 2>&1 | tail -8
-timeout 300 python tools/probe_mmap_register.py 2000 > gpurun_out/probe_mmap.json 2> gpurun_out/probe_mmap.err; tail -c 1500 gpurun_out/probe_mmap.json; tail -3 gpurun_out/probe_mmap.err
-timeout 900 python bench.py > gpurun_out/bench_r02a.json 2> gpurun_out/bench_r02a.err; echo "bench rc=$?"; tail -5 gpurun_out/bench_r02a.err; head -c 3000 gpurun_out/bench_r02a.json
+timeout 1700 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
+timeout 900 python bench.py > gpurun_out/bench_r02b.json 2> gpurun_out/bench_r02b.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_r02b.err
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_r02b_ref.json 2> gpurun_out/bench_r02b_ref.err; echo "ref rc=$?"

@@ -1,0 +1,15 @@
+# r02 profile captures (one B200): launch list of the bench command, full captures of the kernels of
+# the headline shape (LibFM u64) and of the CSV shape, each behind a plain run of the same command
+set -e
+CMD="python bench.py --gb 2 --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-shapes"
+$CMD > gpurun_out/prof_plain.json 2> gpurun_out/prof_plain.err && \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_launches.csv $CMD > gpurun_out/prof_l.log 2>&1
+$CMD > gpurun_out/prof_plain.json 2> gpurun_out/prof_plain.err && \
+ncu --set full --clock-control none --import-source on -k regex:Ranges -s 12 -c 2 -o gpurun_out/r02_split_libfm -f $CMD > gpurun_out/prof_a.log 2>&1
+CMD2="$CMD --shape 1"
+$CMD2 > gpurun_out/prof_plain2.json 2> gpurun_out/prof_plain2.err && \
+ncu --set full --clock-control none --import-source on -k regex:ParseTiles -s 6 -c 1 -o gpurun_out/r02_tiles_csv -f $CMD2 > gpurun_out/prof_b.log 2>&1
+CMD3="$CMD --shape 0"
+$CMD3 > gpurun_out/prof_plain3.json 2> gpurun_out/prof_plain3.err && \
+ncu --set full --clock-control none --import-source on -k regex:Ranges -s 12 -c 2 -o gpurun_out/r02_split_libsvm -f $CMD3 > gpurun_out/prof_c.log 2>&1
+tail -2 gpurun_out/prof_a.log gpurun_out/prof_b.log gpurun_out/prof_c.log
