@@ -203,8 +203,10 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
         /* one 16-bit store per token, into the queue of its role; the queues' running ends are
            kept as offsets into the range's block */
         const uint16_t rel = static_cast<uint16_t>(r.at - lo);
-        if ((r.m_index & me) != 0u) q16[n_index + __popc(r.m_index & lt)] = rel;
-        if ((r.m_value & me) != 0u) q16[v_end - __popc(r.m_value & lt)] = rel;
+        const uint32_t k_index = n_index + __popc(r.m_index & lt);
+        const uint32_t k_value = v_end - __popc(r.m_value & lt);
+        const bool is_index = (r.m_index & me) != 0u, is_value = (r.m_value & me) != 0u;
+        if (is_index || is_value) q16[is_index ? k_index : k_value] = rel;    /* a token is never both */
         if (r.m_label != 0u) {           /* a row starts in this group */
           if ((r.m_label & me) != 0u) {
             const uint32_t k = n_rows + __popc(r.m_label & lt);
@@ -230,7 +232,7 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
           /* the field id of an entry is the token in front of its index token */
           uint32_t prev_at = __shfl_up_sync(0xffffffffu, r.at, 1);
           if (lane == 0) prev_at = carry_at;
-          if ((r.m_index & me) != 0u) q16[at.field + n_index + __popc(r.m_index & lt)] = static_cast<uint16_t>(prev_at - lo);
+          if (is_index) q16[at.field + k_index] = static_cast<uint16_t>(prev_at - lo);
           carry_at = __shfl_sync(0xffffffffu, r.at, static_cast<int>(count) - 1);
         }
         if (FMT == kLibSVM && r.m_qid != 0u) {
