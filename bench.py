@@ -623,7 +623,7 @@ def main():
     # The path's algorithmic bytes (text read once, every array element written once) are
     # the work of ALL its launches on a chunk, so the headline fraction divides them by the summed
     # kernel time; the dominant launch is shown beside it with the bytes it moves itself.
-    traffic = [ncu_traffic(k) for k in names if k]
+    traffic = [ncu_traffic(k) for k in names if "<" in k]       # the two scan launches move kilobytes
     scaled = [t["bytes_per_launch"] * (n / t["captured_on_bytes"]) if t and t.get("captured_on_bytes") else
               (t["bytes_per_launch"] if t else None) for t in traffic]
     achieved = b_alg / (total_ms * 1e-3) / GB
