@@ -31,6 +31,18 @@
 
 namespace b200p {
 
+/* checked build (-DB200P_CHECKED): every queue write and every CSR store of these kernels is
+   bounds-checked; a violation sets kErrInternal instead of writing (see text_kernels.cuh) */
+#ifdef B200P_CHECKED
+#define B200P_SPLIT_CHECK(sp, cond) \
+  if (!(cond)) { atomicOr((sp).give_up, static_cast<uint32_t>(kErrInternal)); } else
+#define B200P_OUT_CHECK(prm, cond) \
+  if (!(cond)) { atomicOr(&(prm).summary->error, static_cast<unsigned int>(kErrInternal)); } else
+#else
+#define B200P_SPLIT_CHECK(sp, cond)
+#define B200P_OUT_CHECK(prm, cond)
+#endif
+
 struct SplitParams {
   WalkParams walk;          /* text, ranges, counts / tile_base / summary, outputs: as for the walk */
   uint16_t *queues;         /* num_ranges blocks of queue_stride entries */
@@ -175,6 +187,7 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
       while (bits != 0u) {
         const uint32_t b = __ffs(bits) - 1;
         bits &= bits - 1u;
+        B200P_SPLIT_CHECK(sp, slot < kTokenQueue)
         tokens[slot] = first4 + b + SeparatorKind(__funnelshift_r(p_lo, p_mid, b) & 0xffu);
         ++slot;
       }
@@ -182,6 +195,7 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
       while (bits != 0u) {
         const uint32_t b = __ffs(bits) - 1;
         bits &= bits - 1u;
+        B200P_SPLIT_CHECK(sp, slot < kTokenQueue)
         tokens[slot] = first4 + 32u + b + SeparatorKind(__funnelshift_r(p_mid, p_hi, b) & 0xffu);
         ++slot;
       }
@@ -206,12 +220,17 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
         const uint32_t k_index = n_index + __popc(r.m_index & lt);
         const uint32_t k_value = v_end - __popc(r.m_value & lt);
         const bool is_index = (r.m_index & me) != 0u, is_value = (r.m_value & me) != 0u;
-        if (is_index || is_value) q16[is_index ? k_index : k_value] = rel;    /* a token is never both */
+        if (is_index || is_value) {
+          B200P_SPLIT_CHECK(sp, (is_index ? k_index : k_value) < sp.cap_pool && k_index <= k_value + 1u)
+          q16[is_index ? k_index : k_value] = rel;    /* a token is never both */
+        }
         if (r.m_label != 0u) {           /* a row starts in this group */
           if ((r.m_label & me) != 0u) {
             const uint32_t k = n_rows + __popc(r.m_label & lt);
-            q16[at.row_at + k] = rel;
-            q16[at.row_nnz + k] = static_cast<uint16_t>(n_index + __popc(r.m_index & lt));
+            B200P_SPLIT_CHECK(sp, k < sp.cap_rows) {
+              q16[at.row_at + k] = rel;
+              q16[at.row_nnz + k] = static_cast<uint16_t>(n_index + __popc(r.m_index & lt));
+            }
           }
           n_rows += __popc(r.m_label);
           if (r.m_weight != 0u) {
@@ -232,7 +251,10 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
           /* the field id of an entry is the token in front of its index token */
           uint32_t prev_at = __shfl_up_sync(0xffffffffu, r.at, 1);
           if (lane == 0) prev_at = carry_at;
-          if (is_index) q16[at.field + k_index] = static_cast<uint16_t>(prev_at - lo);
+          if (is_index) {
+            B200P_SPLIT_CHECK(sp, k_index < sp.cap_pool / 2u && at.field + k_index < sp.queue_stride)
+            q16[at.field + k_index] = static_cast<uint16_t>(prev_at - lo);
+          }
           carry_at = __shfl_sync(0xffffffffu, r.at, static_cast<int>(count) - 1);
         }
         if (FMT == kLibSVM && r.m_qid != 0u) {
@@ -301,6 +323,11 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams
   const SplitOffsets at = SplitLayout<FMT>(sp.cap_pool, sp.cap_rows);
   IdxT *const index = reinterpret_cast<IdxT *>(prm.index);
 
+  bool neg = false;
+  B200P_OUT_CHECK(prm, b[kRows] + n[kRows] <= sum->total[kRows] && b[kNnz] + n[kNnz] <= sum->total[kNnz] &&
+                           b[kValues] + n[kValues] <= sum->total[kValues] && b[kWeights] + n[kWeights] <= sum->total[kWeights] &&
+                           b[kQids] + n[kQids] <= sum->total[kQids] && n[kNnz] + n[kValues] <= sp.cap_pool &&
+                           n[kRows] <= sp.cap_rows) {
   for (uint32_t i = lane; i < n[kRows]; i += 32u) {
     prm.label[b[kRows] + i] = ToFloatFast(txt, lo + q16[at.row_at + i]);
     prm.offset[b[kRows] + i] = static_cast<unsigned long long>(b[kNnz] + q16[at.row_nnz + i]);
@@ -318,7 +345,6 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams
      queue entries of the next trip are read one trip ahead and the text they point at is
      requested from L2 (prefetch), so that neither the queue read nor the token windows of a trip
      wait for memory. */
-  bool neg = false;
   const uint32_t sweep = max(n[kNnz], n[kValues]);
   const uint8_t *const text_lo = prm.text + lo;
   const auto prefetch = [&](uint32_t rel) {
@@ -350,6 +376,7 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams
     a_index = b_index; a_field = b_field; a_value = b_value;
     b_index = c_index; b_field = c_field; b_value = c_value;
   }
+  }   /* B200P_OUT_CHECK */
   if (__any_sync(0xffffffffu, neg) && lane == 0) atomicOr(&prm.summary->error, static_cast<unsigned int>(kErrNegativeIndex));
 }
 
