@@ -75,6 +75,7 @@ class TextSplit : public InputSplit, public LineSource {
     std::string path;
     uint64_t size;
     int fd;
+    const char *map;   /* read-only mapping of the file (DMLC_B200_READ_MMAP=1), else NULL */
   };
   void ExpandUri(const std::string &uri);
   void AddPath(const std::string &path, bool from_listing);
