@@ -399,6 +399,22 @@ __device__ __forceinline__ void DrainRoleQueues(const WalkParams &prm, const Tex
  * of a line positions 1,2 are label, weight (libsvm_parser.h:50-61); everything after that is
  * consumed in groups of 2 (index[:value]) or 3 (field:index[:value]).
  */
+/* true when the six bytes in front of position `at` are "<digit-run byte> qid:" -- the one longer
+   separator well-formed ranking data has on every row (libsvm_parser.h:66-75).  Two aligned word
+   pairs instead of six byte loads behind short-circuit tests: one trip to memory, not six. */
+__device__ __forceinline__ bool QidBehind(const Text &txt, uint32_t at) {
+  if (at < 8u || ((at - 8u) & ~3u) + 12u > txt.size) {
+    if (at < 6u) return false;
+    const uint32_t c1 = txt.at(at - 1u), c2 = txt.at(at - 2u), c3 = txt.at(at - 3u), c4 = txt.at(at - 4u),
+                   c5 = txt.at(at - 5u), c6 = txt.at(at - 6u);
+    return c1 == ':' && c2 == 'd' && c3 == 'i' && c4 == 'q' && c5 == ' ' && IsDigitChar(c6);
+  }
+  const uint32_t p = at - 8u, a = p & ~3u, k = p & 3u;
+  const uint32_t w0 = Load4(txt.data + a), w1 = Load4(txt.data + a + 4), w2 = Load4(txt.data + a + 8);
+  const uint32_t x0 = BytesFrom(w0, w1, k), x1 = BytesFrom(w1, w2, k);   /* bytes at-8..at-5, at-4..at-1 */
+  return x1 == 0x3a646971u /* "qid:" */ && (x0 >> 24) == ' ' && IsDigitChar((x0 >> 16) & 0xffu);
+}
+
 struct GroupRoles {
   uint32_t m_label, m_weight, m_index, m_value, m_qid, m_field; /* bit i = token i of the group */
   uint32_t at;          /* this lane's token: byte position */
@@ -427,10 +443,7 @@ __device__ __forceinline__ GroupRoles TokenRoles(const Text &txt, const uint32_t
   bool qid_number = false;
   uint32_t qid_numbers = 0u;
   if (QID && FMT == kLibSVM && general_m != 0u) {
-    if (general && at >= 6u) {
-      qid_number = txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
-                   txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u));
-    }
+    if (general) qid_number = QidBehind(txt, at);
     qid_numbers = __ballot_sync(0xffffffffu, qid_number);
   }
 
@@ -493,10 +506,8 @@ __device__ __forceinline__ GroupRoles TokenRoles(const Text &txt, const uint32_t
       /* the one longer separator that well-formed ranking data has on every row,
          "<digit-run byte> qid:" (libsvm_parser.h:66-75), is recognised without the walk */
       bool walk = general;
-      if (FMT == kLibSVM && general && at >= 6u) {
-        if (QID ? qid_number
-                : (txt.at(at - 1u) == ':' && txt.at(at - 2u) == 'd' && txt.at(at - 3u) == 'i' &&
-                   txt.at(at - 4u) == 'q' && txt.at(at - 5u) == ' ' && IsDigitChar(txt.at(at - 6u)))) {
+      if (FMT == kLibSVM && general) {
+        if (QID ? qid_number : QidBehind(txt, at)) {
           line_start = false;
           bound = false;            /* first non-blank of the separator is 'q' */
           qid_a = qid_b = true;     /* one space, then "qid:": both probe variants match */
