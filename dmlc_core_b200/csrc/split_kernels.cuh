@@ -347,10 +347,10 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams
      wait for memory. */
   const uint32_t sweep = max(n[kNnz], n[kValues]);
   const uint8_t *const text_lo = prm.text + lo;
+  const uint32_t last_rel = prm.size - 1u - lo;       /* prefetches stay inside the chunk */
   const auto prefetch = [&](uint32_t rel) {
-    const uint8_t *p = text_lo + rel;
-    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
-    asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 20));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(text_lo + rel));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(text_lo + min(rel + 20u, last_rel)));
   };
   /* pipeline: positions of trip t+1 (a*) and t+2 (b*) are in registers, those of t+3 are being
      read; the text of trip t+2 is requested while trip t is converted */
@@ -516,15 +516,16 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertFieldRanges(const SplitP
   const bool labelled = prm.label_column == 0;
   IdxT *const index = reinterpret_cast<IdxT *>(prm.index);
 
-  /* values: queue entries one trip ahead, their text requested from L2 meanwhile */
+  /* values: queue entries three trips ahead, their text requested from L2 two trips ahead */
   const uint8_t *const text_lo = prm.text + lo;
+  const uint32_t last_rel = prm.size - 1u - lo;       /* prefetches stay inside the chunk */
   const auto value_at = [&](uint32_t k) -> uint32_t { return k < n_value ? q16[k] : 0u; };
   uint32_t p_value = value_at(lane), a_value = value_at(lane + 32u), b_value = value_at(lane + 64u);
   for (uint32_t i = lane; i < n_value; i += 32u) {
     const uint32_t c_value = value_at(i + 96u);
     if (i + 64u < n_value) {
       asm volatile("prefetch.global.L1 [%0];" ::"l"(text_lo + b_value));
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(text_lo + b_value + 20));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(text_lo + min(b_value + 20u, last_rel)));
     }
     prm.value[b_nnz + i] = ToFloatFast(txt, lo + p_value);
     p_value = a_value;

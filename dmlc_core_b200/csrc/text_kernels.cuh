@@ -461,7 +461,7 @@ __device__ __forceinline__ GroupRoles TokenRoles(const Text &txt, const uint32_t
        ballots -- no per-lane chain walk.  Longer chains and unusual separators take the general
        code below; both implement the same rules (the checked build verifies that pass 2
        produces exactly what pass 1 counted, range by range). */
-    const uint32_t act_m = count >= 32u ? 0xffffffffu : ((1u << count) - 1u);
+    const uint32_t act_m = 0xffffffffu >> (32u - count);   /* count is 1..32 */
     const uint32_t line_m = __ballot_sync(0xffffffffu, active && kind == 3u);
     const uint32_t bound_m = __ballot_sync(0xffffffffu, active && kind == 1u);
     const uint32_t start_m = act_m & ~bound_m;                    /* chain position 1 */

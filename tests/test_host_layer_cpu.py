@@ -164,8 +164,9 @@ def test_large_chunks_go_through_the_reader_pool(hostapi, tmp_path, monkeypatch)
     assert len(text) > 18 << 20
     f = tmp_path / "big.txt"
     f.write_bytes(text)
-    for threads in ("3", "1", "7"):
+    for threads, use_map in (("3", "1"), ("1", "1"), ("7", "0"), ("2", "0")):   # mmap + streaming stores / pread
         monkeypatch.setenv("DMLC_B200_READ_THREADS", threads)
+        monkeypatch.setenv("DMLC_B200_READ_MMAP", use_map)
         whole, pieces = hostapi.split_bytes(str(f), 0, 1, mode=0, chunk_hint=9 << 20, cap=len(text) + 64)
         assert whole == text and 2 <= pieces <= 4
     parts = [hostapi.split_bytes(str(f), k, 3, mode=0, chunk_hint=5 << 20, cap=len(text) + 64)[0] for k in range(3)]
