@@ -98,10 +98,13 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
   if (range >= prm.num_ranges) return;
   uint32_t *const tokens = rings[warp];
   const Text txt = {prm.text, prm.size};
-  uint16_t *const q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  uint16_t *q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
   const SplitOffsets at = SplitLayout<FMT>(sp.cap_pool, sp.cap_rows);
 
-  const uint32_t lo = range * prm.range_bytes;
+  uint32_t lo = range * prm.range_bytes;
+  /* held in registers: left to itself the compiler rebuilds the block's address (a 64-bit
+     multiply-add and two adds) and `lo` from the kernel parameters at every store of the loop */
+  asm volatile("" : "+l"(q16), "+r"(lo));
   const uint32_t hi = min(lo + prm.range_bytes, prm.size);
   uint32_t n_rows = 0, n_index = 0, n_value = 0, n_weight = 0, n_qid = 0;
   uint32_t error = 0;
@@ -124,7 +127,6 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
     const uint32_t lt = LaneMaskLt();
     const uint32_t me = 1u << lane;
     const uint8_t *const my_text = prm.text + 16u * lane;
-    const uint32_t room_pool = sp.cap_pool - 64u, room_rows = sp.cap_rows - 32u, room_field = sp.cap_pool / 2u - 32u;
     uint32_t v_end = sp.cap_pool - 1u;    /* value entries grow down from the end of the pool */
 
     /* the text of an interior step is requested one step ahead, so that the trip to HBM is spent
@@ -202,17 +204,19 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
       fill += __shfl_sync(0xffffffffu, incl, 31);
       __syncwarp();
 
+      /* room for whatever the queued tokens turn out to be: each of them adds at most one entry
+         to the pool, to the row queues, to the field queue */
+      if (n_index + n_value + fill > sp.cap_pool || n_rows + fill > sp.cap_rows ||
+          (FMT == kLibFM && n_index + fill > sp.cap_pool / 2u)) {
+        give_up = true;
+        dense = true;
+        break;
+      }
       /* full groups of 32 tokens (all of them once the owned lines are finished) */
       uint32_t head = 0;
       const uint32_t groups = done ? (fill + 31u) >> 5 : fill >> 5;
       for (uint32_t g = 0; g < groups; ++g) {
         const uint32_t count = min(fill - head, 32u);
-        if (n_index + n_value > room_pool || n_rows > room_rows || (FMT == kLibFM && n_index > room_field)) {
-          give_up = true;
-          dense = true;
-          done = true;
-          break;
-        }
         const GroupRoles r = TokenRoles<FMT, QID>(txt, tokens, head, count, lane, carry_pos, carry_first);
         /* one 16-bit store per token, into the queue of its role; the queues' running ends are
            kept as offsets into the range's block */
@@ -269,7 +273,7 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
         carry_first = r.next_first;
         head += count;
       }
-      if (head != 0u && !give_up) {
+      if (head != 0u) {
         const uint32_t rest = fill - head;
         uint32_t moved = 0;
         if (lane < rest) moved = tokens[head + lane];
@@ -319,7 +323,8 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams
   }
   const Text txt = {prm.text, prm.size};
   const uint32_t lo = range * prm.range_bytes;
-  const uint16_t *const q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  const uint16_t *q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  asm volatile("" : "+l"(q16));     /* kept in registers, see CollectRanges */
   const SplitOffsets at = SplitLayout<FMT>(sp.cap_pool, sp.cap_rows);
   IdxT *const index = reinterpret_cast<IdxT *>(prm.index);
 
@@ -403,7 +408,8 @@ __global__ void __launch_bounds__(kSplitThreads) CollectFieldRanges(const SplitP
   const int lane = threadIdx.x & 31;
   const uint32_t range = blockIdx.x * kSplitWarps + (threadIdx.x >> 5);
   if (range >= prm.num_ranges) return;
-  uint16_t *const q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  uint16_t *q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  asm volatile("" : "+l"(q16));     /* kept in registers, see CollectRanges */
   const uint32_t o_row_at = sp.cap_pool, o_row_nnz = sp.cap_pool + sp.cap_rows, o_meta = sp.cap_pool + 2u * sp.cap_rows;
   const uint32_t lo = range * prm.range_bytes;
   const uint32_t hi = min(lo + prm.range_bytes, prm.size);
@@ -511,7 +517,8 @@ __global__ void __launch_bounds__(kSplitThreads) ConvertFieldRanges(const SplitP
   const uint32_t n_value = static_cast<uint32_t>(start_of(kNnz, range + 1u)) - b_nnz;
   const Text txt = {prm.text, prm.size};
   const uint32_t lo = range * prm.range_bytes;
-  const uint16_t *const q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  const uint16_t *q16 = sp.queues + static_cast<size_t>(range) * sp.queue_stride;
+  asm volatile("" : "+l"(q16));     /* kept in registers, see CollectRanges */
   const uint32_t o_row_at = sp.cap_pool, o_row_nnz = sp.cap_pool + sp.cap_rows, o_meta = sp.cap_pool + 2u * sp.cap_rows;
   const bool labelled = prm.label_column == 0;
   IdxT *const index = reinterpret_cast<IdxT *>(prm.index);
