@@ -81,7 +81,8 @@ constexpr int kSplitThreads = kSplitWarps * 32;
 /* resident CTAs per SM the register budget of CollectRanges is held to.  Measured on B200 (500 MB
    per shape, ms per launch, LibSVM / LibFM u64 / Criteo): 4 CTAs (64 registers) 0.586 / 0.666 /
    0.617, 5 CTAs (48) 0.642 / 0.710 / 0.664, 6 CTAs (40) 0.662 / 0.775 / 0.686 -- the spills cost
-   more instructions than the extra warps hide. */
+   more instructions than the extra warps hide; 3 CTAs (80 registers, no value rebuilt) are 8 %
+   slower than 4: the kernel wants its 32 warps. */
 #ifndef B200P_COLLECT_CTAS
 #define B200P_COLLECT_CTAS 4
 #endif
@@ -89,8 +90,15 @@ template <int FMT, typename IdxT, bool QID>
 __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRanges(const SplitParams sp) {
   __shared__ uint32_t rings[kSplitWarps][kTokenQueue];
   __shared__ __align__(16) uint8_t lut[256];
+  /* separator kind by the class nibbles of the two bytes in front of a token: one LDS per token
+     where SeparatorKind() costs seven instructions, five of them on the ALU pipe that bounds
+     this kernel */
+  __shared__ __align__(16) uint8_t kind_of[256];
   const WalkParams &prm = sp.walk;
-  for (int c = threadIdx.x; c < 256; c += kSplitThreads) lut[c] = static_cast<uint8_t>(ClassEntry<FMT>(c));
+  for (int c = threadIdx.x; c < 256; c += kSplitThreads) {
+    lut[c] = static_cast<uint8_t>(ClassEntry<FMT>(c));
+    kind_of[c] = static_cast<uint8_t>(SeparatorKind(c));
+  }
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -146,6 +154,13 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
       if (interior) {
         ClassifyLut4(now, lut, prm.sixteen, &m0, &m1);
       } else {
+        if (base + kStepBytes - lo > 0xffffu) {
+          /* positions are stored as 16-bit offsets from `lo`: a line that carries the range past
+             64 KiB is left to the two-pass kernels (a range is at most 32 KiB, so only a step
+             behind its last byte -- never an interior one -- can get there) */
+          give_up = true;
+          break;
+        }
         ClassifyLut4(Load16(prm.text, prm.size, first_byte), lut, prm.sixteen, &m0, &m1);
         const uint32_t cm = KeepMask(first_byte, hi - 1u, prm.size);
         const uint32_t c0 = (m0 >> 1) & kNibD & SpreadNibbles8(cm & 0xffu);
@@ -168,12 +183,6 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
         k0 = SpreadNibbles8(km & 0xffu);
         k1 = SpreadNibbles8(km >> 8);
       }
-      if (base + kStepBytes - lo > 0xffffu) {
-        /* positions are stored as 16-bit offsets from `lo`: a line that carries the range past
-           64 KiB is left to the two-pass kernels */
-        give_up = true;
-        break;
-      }
       uint32_t up = __shfl_up_sync(0xffffffffu, m1 >> 24, 1);
       if (lane == 0) up = carry;
       carry = __shfl_sync(0xffffffffu, m1 >> 24, 31);
@@ -185,20 +194,23 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
       uint32_t slot = fill + incl - mine;
       const uint32_t p_lo = up | (m0 << 8), p_mid = (m0 >> 24) | (m1 << 8), p_hi = m1 >> 24;
       const uint32_t first4 = 4u * first_byte;
+      /* rolled: unrolled sevenfold (the compiler's choice) the two loops run 1-3 % slower */
       uint32_t bits = s0;
+#pragma unroll 1
       while (bits != 0u) {
         const uint32_t b = __ffs(bits) - 1;
         bits &= bits - 1u;
         B200P_SPLIT_CHECK(sp, slot < kTokenQueue)
-        tokens[slot] = first4 + b + SeparatorKind(__funnelshift_r(p_lo, p_mid, b) & 0xffu);
+        tokens[slot] = first4 + b + kind_of[__funnelshift_r(p_lo, p_mid, b) & 0xffu];
         ++slot;
       }
       bits = s1;
+#pragma unroll 1
       while (bits != 0u) {
         const uint32_t b = __ffs(bits) - 1;
         bits &= bits - 1u;
         B200P_SPLIT_CHECK(sp, slot < kTokenQueue)
-        tokens[slot] = first4 + 32u + b + SeparatorKind(__funnelshift_r(p_mid, p_hi, b) & 0xffu);
+        tokens[slot] = first4 + 32u + b + kind_of[__funnelshift_r(p_mid, p_hi, b) & 0xffu];
         ++slot;
       }
       fill += __shfl_sync(0xffffffffu, incl, 31);
@@ -228,22 +240,26 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
           B200P_SPLIT_CHECK(sp, (is_index ? k_index : k_value) < sp.cap_pool && k_index <= k_value + 1u)
           q16[is_index ? k_index : k_value] = rel;    /* a token is never both */
         }
-        if (r.m_label != 0u) {           /* a row starts in this group */
-          if ((r.m_label & me) != 0u) {
-            const uint32_t k = n_rows + __popc(r.m_label & lt);
-            B200P_SPLIT_CHECK(sp, k < sp.cap_rows) {
-              q16[at.row_at + k] = rel;
-              q16[at.row_nnz + k] = static_cast<uint16_t>(n_index + __popc(r.m_index & lt));
+        /* label, weight, qid: one test for the groups that hold none of them */
+        if ((r.m_label | r.m_weight | (FMT == kLibSVM ? r.m_qid : 0u)) != 0u) {
+          if (r.m_label != 0u) {           /* a row starts in this group */
+            if ((r.m_label & me) != 0u) {
+              const uint32_t k = n_rows + __popc(r.m_label & lt);
+              B200P_SPLIT_CHECK(sp, k < sp.cap_rows) {
+                q16[at.row_at + k] = rel;
+                q16[at.row_nnz + k] = static_cast<uint16_t>(n_index + __popc(r.m_index & lt));
+              }
             }
+            n_rows += __popc(r.m_label);
           }
-          n_rows += __popc(r.m_label);
           if (r.m_weight != 0u) {
             if ((r.m_weight & me) != 0u) q16[at.weight + n_weight + __popc(r.m_weight & lt)] = rel;
             n_weight += __popc(r.m_weight);
           }
-        } else if (r.m_weight != 0u) {   /* label and weight fell into different groups */
-          if ((r.m_weight & me) != 0u) q16[at.weight + n_weight + __popc(r.m_weight & lt)] = rel;
-          n_weight += __popc(r.m_weight);
+          if (FMT == kLibSVM && r.m_qid != 0u) {
+            if ((r.m_qid & me) != 0u) q16[at.qid + n_qid + __popc(r.m_qid & lt)] = static_cast<uint16_t>(r.qid_at - lo);
+            n_qid += __popc(r.m_qid);
+          }
         }
         if (FMT == kLibFM) {
           /* a '-' on a field id raises even when the triple is dropped (libfm_parser.h:73);
@@ -260,10 +276,6 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
             q16[at.field + k_index] = static_cast<uint16_t>(prev_at - lo);
           }
           carry_at = __shfl_sync(0xffffffffu, r.at, static_cast<int>(count) - 1);
-        }
-        if (FMT == kLibSVM && r.m_qid != 0u) {
-          if ((r.m_qid & me) != 0u) q16[at.qid + n_qid + __popc(r.m_qid & lt)] = static_cast<uint16_t>(r.qid_at - lo);
-          n_qid += __popc(r.m_qid);
         }
         n_index += __popc(r.m_index);
         const uint32_t nv = __popc(r.m_value);
