@@ -310,8 +310,14 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
 }
 
 /* the queues of CollectRanges drained into the CSR arrays */
+/* resident CTAs per SM the register budget of the convert kernels is held to: 6 (40 registers,
+   48 warps) against the 46 registers / 5 CTAs the u64 instantiations take when left alone is worth
+   1-2 % on LibSVM; 8 (32 registers, spills) costs 7-14 % */
+#ifndef B200P_CONVERT_CTAS
+#define B200P_CONVERT_CTAS 6
+#endif
 template <int FMT, typename IdxT>
-__global__ void __launch_bounds__(kSplitThreads) ConvertRanges(const SplitParams sp) {
+__global__ void __launch_bounds__(kSplitThreads, B200P_CONVERT_CTAS) ConvertRanges(const SplitParams sp) {
   const WalkParams &prm = sp.walk;
   const int lane = threadIdx.x & 31;
   const uint32_t range = blockIdx.x * kSplitWarps + (threadIdx.x >> 5);
@@ -507,7 +513,7 @@ __global__ void __launch_bounds__(kSplitThreads) CollectFieldRanges(const SplitP
 }
 
 template <typename IdxT>
-__global__ void __launch_bounds__(kSplitThreads) ConvertFieldRanges(const SplitParams sp) {
+__global__ void __launch_bounds__(kSplitThreads, B200P_CONVERT_CTAS) ConvertFieldRanges(const SplitParams sp) {
   const WalkParams &prm = sp.walk;
   const int lane = threadIdx.x & 31;
   const uint32_t range = blockIdx.x * kSplitWarps + (threadIdx.x >> 5);
