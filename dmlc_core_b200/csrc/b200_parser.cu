@@ -256,9 +256,26 @@ namespace {
 std::mutex g_registered_mu;
 struct Registered {
   void *ptr;
-  int device;   /* current when the block was pinned; made current again to unpin it */
+  int device;        /* current when the block was pinned; made current again to unpin it */
+  uint64_t bytes;    /* size of the block (a multiple of 2 MiB) */
 };
-std::vector<Registered> g_registered;   /* blocks obtained through the register path */
+std::vector<Registered> g_registered;   /* blocks obtained through the register path, in use */
+/* Blocks a destroyed handle gave back, kept pinned for the next one: zero-filling, pinning and
+   unpinning the 0.4-0.6 GB of a pipeline cost 35-50 ms each way (tools/first_pass.py), which is
+   most of what a second parser of the same process spends on a file of a few hundred MB.
+   B200P_PIN_CACHE_MB bounds what is kept (default 1024, 0 = nothing); blocks over 256 MiB (the
+   arrays of an in-memory iterator) are never kept.  The blocks are pinned portably, so a
+   handle on another device can take them. */
+std::vector<Registered> g_pin_cache;
+uint64_t g_pin_cache_bytes = 0;
+uint64_t PinCacheLimit() {
+  static const uint64_t limit = [] {
+    const char *v = std::getenv("B200P_PIN_CACHE_MB");
+    const long long mb = (v != NULL && v[0] != '\0') ? std::atoll(v) : 1024;
+    return static_cast<uint64_t>(mb < 0 ? 0 : mb) << 20;
+  }();
+  return limit;
+}
 
 bool HugePagesOnOffer() {
   static const bool on = [] {
@@ -302,6 +319,27 @@ static cudaError_t PinnedAlloc(void **out, uint64_t bytes) {
   if (bytes >= kHuge && HugePagesOnOffer()) {
     void *p = NULL;
     const uint64_t rounded = (bytes + kHuge - 1) / kHuge * kHuge;
+    {
+      /* the smallest kept block that fits and is not more than twice too large */
+      std::lock_guard<std::mutex> g(g_registered_mu);
+      size_t best = g_pin_cache.size();
+      for (size_t i = 0; i < g_pin_cache.size(); ++i) {
+        const uint64_t have = g_pin_cache[i].bytes;
+        if (have >= rounded && have <= 2 * rounded &&
+            (best == g_pin_cache.size() || have < g_pin_cache[best].bytes)) {
+          best = i;
+        }
+      }
+      if (best != g_pin_cache.size()) {
+        const Registered r = g_pin_cache[best];
+        g_pin_cache.erase(g_pin_cache.begin() + static_cast<long>(best));
+        g_pin_cache_bytes -= r.bytes;
+        g_registered.push_back(r);
+        g_pinned_bytes -= bytes;      /* not a fresh allocation */
+        *out = r.ptr;
+        return cudaSuccess;
+      }
+    }
     if (posix_memalign(&p, kHuge, rounded) == 0) {
 #ifdef MADV_HUGEPAGE
       madvise(p, rounded, MADV_HUGEPAGE);
@@ -322,7 +360,7 @@ static cudaError_t PinnedAlloc(void **out, uint64_t bytes) {
         for (std::thread &th : crew) th.join();
       }
       if (cudaHostRegister(p, rounded, cudaHostRegisterPortable) == cudaSuccess) {
-        Registered r = {p, 0};
+        Registered r = {p, 0, rounded};
         if (cudaGetDevice(&r.device) != cudaSuccess) r.device = 0;
         std::lock_guard<std::mutex> g(g_registered_mu);
         g_registered.push_back(r);
@@ -343,8 +381,14 @@ static void PinnedFree(void *p) {
     std::lock_guard<std::mutex> g(g_registered_mu);
     for (size_t i = 0; i < g_registered.size(); ++i) {
       if (g_registered[i].ptr == p) {
-        device = g_registered[i].device;
+        const Registered r = g_registered[i];
         g_registered.erase(g_registered.begin() + static_cast<long>(i));
+        if (r.bytes <= (256ull << 20) && g_pin_cache_bytes + r.bytes <= PinCacheLimit()) {
+          g_pin_cache.push_back(r);
+          g_pin_cache_bytes += r.bytes;
+          return;
+        }
+        device = r.device;
         break;
       }
     }

@@ -656,3 +656,38 @@ def test_copies_come_home_while_the_consumer_is_busy(cuda_lib, oracle):
         walls.setdefault(on_demand, []).append(wall)
     eager, lazy = min(walls[False]), min(walls[True])
     assert eager < lazy - 0.004, (eager, lazy)
+
+
+_TWO_PARSERS = r"""
+import sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from dmlc_core_b200 import capi, datagen
+data, rows = datagen.generate("libsvm", 5, 24 << 20)
+for _ in range(2):
+    p = capi.Parser("libsvm", index_bytes=4, chunk_bytes=32 << 20, depth=2)
+    blk = p.parse_host(data)
+    assert len(blk["label"]) == rows
+    p.close()
+"""
+
+
+@pytest.mark.parametrize("cache_mb", ["1024", "0"])
+def test_a_second_parser_takes_the_pinned_blocks_of_the_first(cuda_lib, cache_mb):
+    """b200p_destroy leaves its pinned blocks to the next handle of the process
+    (B200P_PIN_CACHE_MB): the process total of fresh pinned allocations, as B200P_TRACE prints it
+    at every destroy, must not grow with the second parser -- and must grow when the cache is off."""
+    import re
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, B200P_TRACE="1", B200P_PIN_CACHE_MB=cache_mb)
+    r = subprocess.run([sys.executable, "-c", _TWO_PARSERS, root], env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    totals = [float(m) for m in re.findall(r"pinned allocations [0-9.]+ ms for ([0-9.]+) MB", r.stderr)]
+    assert len(totals) == 2, r.stderr[-2000:]
+    if cache_mb == "0":
+        assert totals[1] > 1.5 * totals[0] > 0, totals
+    else:
+        assert totals[1] <= totals[0] + 1.0 and totals[0] > 0, totals
