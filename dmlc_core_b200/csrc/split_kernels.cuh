@@ -75,7 +75,10 @@ __device__ __forceinline__ SplitOffsets SplitLayout(uint32_t cap_pool, uint32_t 
 }
 
 /* what ConvertRanges needs to know about a range besides the five counts of the scan */
-constexpr int kSplitWarps = 8;
+#ifndef B200P_SPLIT_WARPS
+#define B200P_SPLIT_WARPS 8
+#endif
+constexpr int kSplitWarps = B200P_SPLIT_WARPS;
 constexpr int kSplitThreads = kSplitWarps * 32;
 
 /* resident CTAs per SM the register budget of CollectRanges is held to.  Measured on B200 (500 MB
@@ -84,7 +87,7 @@ constexpr int kSplitThreads = kSplitWarps * 32;
    more instructions than the extra warps hide; 3 CTAs (80 registers, no value rebuilt) are 8 %
    slower than 4: the kernel wants its 32 warps. */
 #ifndef B200P_COLLECT_CTAS
-#define B200P_COLLECT_CTAS 4
+#define B200P_COLLECT_CTAS (32 / B200P_SPLIT_WARPS)
 #endif
 template <int FMT, typename IdxT, bool QID>
 __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRanges(const SplitParams sp) {
@@ -314,7 +317,7 @@ __global__ void __launch_bounds__(kSplitThreads, B200P_COLLECT_CTAS) CollectRang
    48 warps) against the 46 registers / 5 CTAs the u64 instantiations take when left alone is worth
    1-2 % on LibSVM; 8 (32 registers, spills) costs 7-14 % */
 #ifndef B200P_CONVERT_CTAS
-#define B200P_CONVERT_CTAS 6
+#define B200P_CONVERT_CTAS (48 / B200P_SPLIT_WARPS)
 #endif
 template <int FMT, typename IdxT>
 __global__ void __launch_bounds__(kSplitThreads, B200P_CONVERT_CTAS) ConvertRanges(const SplitParams sp) {
