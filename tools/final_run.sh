@@ -1,5 +1,6 @@
-# round-end check on one GPU: parity suite, per-kernel times, first-pass decomposition
+# round-end evidence on one GPU: both bench arms and the ncu captures of the final binary
+# (tools/refresh_profiles.sh turns the result into profiles/)
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -q -m gpu -x > gpurun_out/final_tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/final_tests.log
-timeout 600 python tools/bench_formats.py --mb 1000 > gpurun_out/final_formats.jsonl 2> gpurun_out/final_formats.err; echo "formats rc=$?" >> gpurun_out/final_tests.log
-timeout 600 python tools/first_pass.py > gpurun_out/first_pass.log 2>&1; echo "first_pass rc=$?" >> gpurun_out/final_tests.log
+timeout 900 python bench.py --impl reference > gpurun_out/final_bench_reference.json 2> gpurun_out/final_bench_reference.err; echo "ref rc=$?" > gpurun_out/final_tests.log
+timeout 900 python bench.py > gpurun_out/final_bench.json 2> gpurun_out/final_bench.err; echo "bench rc=$?" >> gpurun_out/final_tests.log
+timeout 1500 bash tools/run_profiles.sh > gpurun_out/final_profiles.log 2>&1; echo "profiles rc=$?" >> gpurun_out/final_tests.log
